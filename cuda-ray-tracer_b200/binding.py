@@ -1,0 +1,198 @@
+"""ctypes binding of librt_b200.so (include/rt_b200.h) and a host-side mirror of the reference's
+back-end call surface, /root/reference/include/update.h:6-8:
+
+    init_update(texture, scene)   -> rt_b200_upload_scene
+    update(camera_matrix) -> ms   -> rt_b200_update
+    cleanup_update()              -> rt_b200_destroy
+
+`Renderer` is the re-entrant form (one opaque context per scene); the three module-level functions keep
+one global context exactly like the reference's translation units do (update-cuda.cu:15-27).
+
+There is NO CPU fallback here: if the CUDA library is missing or no device is present every call raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "librt_b200.so")
+
+COUNTER_FIELDS = ("primary_rays", "reflection_rays", "shadow_rays", "hits", "lit",
+                  "tests_plane", "tests_sphere", "tests_quadric", "tests_cubic", "fp64_confirms")
+
+# every symbol include/rt_b200.h declares
+EXPORTS = ("rt_b200_upload_scene", "rt_b200_update", "rt_b200_gather", "rt_b200_destroy", "rt_b200_last_error",
+           "rt_b200_comm_unique_id", "rt_b200_comm_init", "rt_b200_get_counters", "rt_b200_set_option",
+           "rt_b200_get_timing", "rt_b200_get_class_counts", "rt_b200_version")
+
+UNIQUE_ID_BYTES = 128
+
+
+class RtError(RuntimeError):
+    pass
+
+
+class _Counters(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in COUNTER_FIELDS]
+
+
+_lib = None
+
+
+def load_library():
+    """dlopen librt_b200.so (build it first with build.py / __graft_entry__.build()).  Fails loudly."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RtError("{} is missing: run `python cuda-ray-tracer_b200/build.py` (there is no CPU fallback)".format(LIB_PATH))
+    L = C.CDLL(LIB_PATH)
+    vp = C.c_void_p
+    L.rt_b200_upload_scene.argtypes = [C.POINTER(vp), C.c_uint32, C.c_uint32, C.c_double, vp, C.c_uint32, vp,
+                                       C.c_size_t, vp, C.c_size_t, C.c_int, C.c_int, C.c_int]
+    L.rt_b200_update.argtypes = [vp, vp, C.POINTER(C.c_float)]
+    L.rt_b200_gather.argtypes = [vp, vp, C.c_size_t, C.POINTER(vp)]
+    L.rt_b200_destroy.argtypes = [vp]
+    L.rt_b200_last_error.restype = C.c_char_p
+    L.rt_b200_comm_unique_id.argtypes = [vp]
+    L.rt_b200_comm_init.argtypes = [vp, vp]
+    L.rt_b200_get_counters.argtypes = [vp, C.POINTER(_Counters)]
+    L.rt_b200_set_option.argtypes = [vp, C.c_char_p, C.c_int64]
+    L.rt_b200_get_timing.argtypes = [vp, C.POINTER(C.c_float * 2)]
+    L.rt_b200_get_class_counts.argtypes = [vp, C.POINTER(C.c_uint32 * 4)]
+    L.rt_b200_version.restype = C.c_char_p
+    _lib = L
+    return L
+
+
+def _check(rc: int):
+    if rc != 0:
+        raise RtError("rt_b200 error {}: {}".format(rc, load_library().rt_b200_last_error().decode()))
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def comm_unique_id() -> bytes:
+    buf = (C.c_char * UNIQUE_ID_BYTES)()
+    _check(load_library().rt_b200_comm_unique_id(buf))
+    return bytes(buf)
+
+
+class Renderer:
+    """One uploaded scene on one GPU (one rank of `world_size`)."""
+
+    def __init__(self, scene, device: int = 0, rank: int = 0, world_size: int = 1):
+        L = load_library()
+        self.scene = scene
+        self.width, self.height = int(scene.px_width), int(scene.px_height)
+        self._h = C.c_void_p()
+        bg = np.ascontiguousarray(scene.bg_color, dtype=np.float32)
+        objs = np.ascontiguousarray(scene.objects)
+        lights = np.ascontiguousarray(scene.lights)
+        _check(L.rt_b200_upload_scene(C.byref(self._h), self.width, self.height, float(scene.vertical_fov), _dp(bg),
+                                      int(scene.max_reflections), _dp(objs), len(objs), _dp(lights), len(lights),
+                                      int(device), int(rank), int(world_size)))
+
+    # -- update.h:7
+    def update(self, camera_matrix) -> float:
+        m = np.ascontiguousarray(camera_matrix, dtype=np.float64).reshape(16)
+        ms = C.c_float()
+        _check(load_library().rt_b200_update(self._h, _dp(m), C.byref(ms)))
+        return ms.value
+
+    def gather(self, out: np.ndarray | None = None) -> np.ndarray:
+        """Frame as uint8 [H, W, 4], row 0 = bottom of the picture."""
+        if out is None:
+            out = np.empty((self.height, self.width, 4), dtype=np.uint8)
+        assert out.dtype == np.uint8 and out.flags.c_contiguous
+        _check(load_library().rt_b200_gather(self._h, _dp(out), out.nbytes, None))
+        return out
+
+    def gather_into(self, host_ptr: int, nbytes: int):
+        """Copy the frame into caller-owned host memory (e.g. a pinned torch tensor's data_ptr)."""
+        _check(load_library().rt_b200_gather(self._h, C.c_void_p(host_ptr), nbytes, None))
+
+    def device_frame_ptr(self) -> int:
+        p = C.c_void_p()
+        _check(load_library().rt_b200_gather(self._h, None, 0, C.byref(p)))
+        return p.value
+
+    def comm_init(self, unique_id: bytes):
+        buf = C.create_string_buffer(unique_id, UNIQUE_ID_BYTES)
+        _check(load_library().rt_b200_comm_init(self._h, buf))
+
+    def counters(self) -> dict:
+        c = _Counters()
+        _check(load_library().rt_b200_get_counters(self._h, C.byref(c)))
+        d = {n: int(getattr(c, n)) for n in COUNTER_FIELDS}
+        d["rays"] = d["primary_rays"] + d["reflection_rays"] + d["shadow_rays"]
+        return d
+
+    def set_option(self, name: str, value: int):
+        _check(load_library().rt_b200_set_option(self._h, name.encode(), int(value)))
+
+    def timing(self):
+        t = (C.c_float * 2)()
+        _check(load_library().rt_b200_get_timing(self._h, C.byref(t)))
+        return {"render_ms": t[0], "gather_ms": t[1]}
+
+    def class_counts(self):
+        t = (C.c_uint32 * 4)()
+        _check(load_library().rt_b200_get_class_counts(self._h, C.byref(t)))
+        return {"plane": t[0], "sphere": t[1], "quadric": t[2], "cubic": t[3]}
+
+    # -- update.h:8
+    def close(self):
+        if self._h:
+            load_library().rt_b200_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
+# ---- the reference's three free functions, one global context (update.h:6-8) ------------------------
+_global: Renderer | None = None
+
+
+def init_update(texture, scene, device: int = 0) -> None:
+    """update.h:6.  `texture` (a GL name in the reference) is ignored: the frame is read with gather()."""
+    global _global
+    if _global is not None:
+        _global.close()
+    _global = Renderer(scene, device=device)
+
+
+def update(camera_matrix) -> float:
+    """update.h:7.  Returns the render time in milliseconds, like the reference."""
+    if _global is None:
+        raise RtError("update() before init_update()")
+    return _global.update(camera_matrix)
+
+
+def gather(out=None) -> np.ndarray:
+    if _global is None:
+        raise RtError("gather() before init_update()")
+    return _global.gather(out)
+
+
+def cleanup_update() -> None:
+    """update.h:8."""
+    global _global
+    if _global is not None:
+        _global.close()
+        _global = None

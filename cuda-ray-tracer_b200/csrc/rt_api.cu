@@ -1,0 +1,490 @@
+// rt_api.cu — implementation of the C ABI declared in include/rt_b200.h.
+//
+// Host-side work per call:
+//   rt_b200_upload_scene  classify + repack the reference's AoS Object[] / LightSource[] into the class-sorted
+//                         SoA of rt_scene.h, upload once, allocate the frame buffers (≙ update-cuda.cu:34-63)
+//   rt_b200_update        fill FrameParams from the camera matrix, launch, optionally all-gather the strips,
+//                         event-time it (≙ update-cuda.cu:160-190)
+//   rt_b200_gather        hand out the assembled RGBA8 frame (replaces the GL texture)
+// No CPU rendering path exists in this library: if CUDA is unavailable the calls fail with RT_B200_ERR_CUDA.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/rt_b200.h"
+#include "rt_kernels.h"
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_last_error = buf;
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                              \
+    do {                                                                                            \
+        cudaError_t e_ = (expr);                                                                    \
+        if (e_ != cudaSuccess) return fail(RT_B200_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(e_)); \
+    } while (0)
+
+// ---- NCCL, loaded on first use (the Python host already has torch's libnccl.so.2 mapped) -----------
+struct NcclApi {
+    void *handle = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+};
+NcclApi g_nccl;
+
+int load_nccl()
+{
+    if (g_nccl.handle) return RT_B200_OK;
+    void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) return fail(RT_B200_ERR_NCCL, "cannot load libnccl.so.2: %s", dlerror());
+    g_nccl.GetUniqueId = (decltype(g_nccl.GetUniqueId)) dlsym(h, "ncclGetUniqueId");
+    g_nccl.CommInitRank = (decltype(g_nccl.CommInitRank)) dlsym(h, "ncclCommInitRank");
+    g_nccl.CommDestroy = (decltype(g_nccl.CommDestroy)) dlsym(h, "ncclCommDestroy");
+    g_nccl.AllGather = (decltype(g_nccl.AllGather)) dlsym(h, "ncclAllGather");
+    g_nccl.GetErrorString = (decltype(g_nccl.GetErrorString)) dlsym(h, "ncclGetErrorString");
+    if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.CommDestroy || !g_nccl.AllGather ||
+        !g_nccl.GetErrorString) {
+        dlclose(h);
+        return fail(RT_B200_ERR_NCCL, "libnccl.so.2 lacks a required symbol");
+    }
+    g_nccl.handle = h;
+    return RT_B200_OK;
+}
+
+#define NCCL_TRY(expr)                                                                                 \
+    do {                                                                                               \
+        ncclResult_t r_ = (expr);                                                                      \
+        if (r_ != ncclSuccess) return fail(RT_B200_ERR_NCCL, "%s: %s", #expr, g_nccl.GetErrorString(r_)); \
+    } while (0)
+
+template <typename T>
+cudaError_t upload(const std::vector<T> &host, T **dev)
+{
+    *dev = nullptr;
+    size_t bytes = sizeof(T) * (host.empty() ? 1 : host.size());
+    cudaError_t e = cudaMalloc((void **) dev, bytes);
+    if (e != cudaSuccess) return e;
+    if (!host.empty()) e = cudaMemcpy(*dev, host.data(), sizeof(T) * host.size(), cudaMemcpyHostToDevice);
+    return e;
+}
+
+} // namespace
+
+struct rt_b200_ctx {
+    int device = 0, rank = 0, world = 1;
+    int width = 0, height = 0;
+    double vertical_fov = 0, aspect = 0, tan_half_fov = 0;
+    float bg[3] = {0, 0, 0};
+    int max_reflections = 0;
+    uint32_t class_counts[4] = {0, 0, 0, 0};
+
+    // device scene
+    rt::SceneView view{};
+    double4 *d_plane = nullptr, *d_sphere = nullptr;
+    float4 *d_sphere_f = nullptr, *d_material = nullptr;
+    double *d_quadric = nullptr, *d_cubic = nullptr, *d_coef_full = nullptr;
+    int *d_orig = nullptr;
+    rt::LightDev *d_lights = nullptr;
+
+    // frame buffers
+    int strip_rows = 8;
+    int local_rows = 0;             // rows of the packed per-rank buffer (padded to whole strips per rank)
+    uchar4 *d_local = nullptr;      // [local_rows][width]; for world == 1 this IS the frame
+    uchar4 *d_gathered = nullptr;   // [world][local_rows][width] (world > 1)
+    uchar4 *d_frame = nullptr;      // [height][width] (world > 1)
+    unsigned long long *d_counters = nullptr;
+    bool buffers_dirty = true;
+
+    int kernel_kind = 0;
+    bool count = true;
+    bool rendered = false;
+
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_render = nullptr, ev_end = nullptr;
+    float ms_render = 0, ms_gather = 0;
+
+    ncclComm_t comm = nullptr;
+};
+
+namespace {
+
+int free_buffers(rt_b200_ctx *c)
+{
+    if (c->d_local) cudaFree(c->d_local);
+    if (c->d_gathered) cudaFree(c->d_gathered);
+    if (c->d_frame) cudaFree(c->d_frame);
+    c->d_local = c->d_gathered = c->d_frame = nullptr;
+    return RT_B200_OK;
+}
+
+int ensure_buffers(rt_b200_ctx *c)
+{
+    if (!c->buffers_dirty) return RT_B200_OK;
+    free_buffers(c);
+    const int n_strips = (c->height + c->strip_rows - 1) / c->strip_rows;
+    const int strips_per_rank = (n_strips + c->world - 1) / c->world;
+    c->local_rows = (c->world == 1) ? c->height : strips_per_rank * c->strip_rows;
+    const size_t row_bytes = sizeof(uchar4) * (size_t) c->width;
+    CUDA_TRY(cudaMalloc((void **) &c->d_local, row_bytes * c->local_rows));
+    if (c->world > 1) {
+        CUDA_TRY(cudaMalloc((void **) &c->d_gathered, row_bytes * c->local_rows * c->world));
+        CUDA_TRY(cudaMalloc((void **) &c->d_frame, row_bytes * c->height));
+        CUDA_TRY(cudaMemsetAsync(c->d_gathered, 0, row_bytes * c->local_rows * c->world, c->stream));
+        CUDA_TRY(cudaMemsetAsync(c->d_frame, 0, row_bytes * c->height, c->stream));
+    }
+    c->buffers_dirty = false;
+    c->rendered = false;
+    return RT_B200_OK;
+}
+
+// Structural class of one object: which coefficients are exactly zero.
+rt::ObjClass classify(const double *k)
+{
+    for (int i = rt::X3; i <= rt::XYZ; i++)
+        if (k[i] != 0.0) return rt::CLS_CUBIC;
+    const bool cross = k[rt::XY] != 0.0 || k[rt::XZ] != 0.0 || k[rt::YZ] != 0.0;
+    const bool squares = k[rt::X2] != 0.0 || k[rt::Y2] != 0.0 || k[rt::Z2] != 0.0;
+    if (!cross && !squares) return rt::CLS_PLANE;
+    if (!cross && k[rt::X2] == 1.0 && k[rt::Y2] == 1.0 && k[rt::Z2] == 1.0) return rt::CLS_SPHERE;
+    return rt::CLS_QUADRIC;
+}
+
+} // namespace
+
+extern "C" {
+
+const char *rt_b200_last_error(void) { return g_last_error.c_str(); }
+
+const char *rt_b200_version(void) { return "rt_b200 0.1 sm_100a"; }
+
+int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_height, double vertical_fov_rad,
+                         const float bg_color[3], uint32_t max_reflections, const void *objects, size_t n_objects,
+                         const void *lights, size_t n_lights, int device, int rank, int world_size)
+{
+    if (!ctx_out) return fail(RT_B200_ERR_ARG, "ctx_out is null");
+    *ctx_out = nullptr;
+    if (px_width == 0 || px_height == 0) return fail(RT_B200_ERR_ARG, "empty frame %ux%u", px_width, px_height);
+    if (!bg_color) return fail(RT_B200_ERR_ARG, "bg_color is null");
+    if ((n_objects && !objects) || (n_lights && !lights)) return fail(RT_B200_ERR_ARG, "null scene array");
+    if (world_size < 1 || rank < 0 || rank >= world_size)
+        return fail(RT_B200_ERR_ARG, "bad rank %d of %d", rank, world_size);
+    if (n_objects > (size_t) 1 << 24 || n_lights > (size_t) 1 << 20) return fail(RT_B200_ERR_ARG, "scene too large");
+
+    int n_dev = 0;
+    CUDA_TRY(cudaGetDeviceCount(&n_dev));
+    if (device < 0 || device >= n_dev) return fail(RT_B200_ERR_CUDA, "no CUDA device %d (found %d)", device, n_dev);
+    CUDA_TRY(cudaSetDevice(device));
+
+    rt_b200_ctx *c = new rt_b200_ctx();
+    c->device = device;
+    c->rank = rank;
+    c->world = world_size;
+    c->width = (int) px_width;
+    c->height = (int) px_height;
+    c->vertical_fov = vertical_fov_rad;
+    c->aspect = (double) px_width / px_height;          // Scene::aspect_ratio, scene.h:32-33
+    c->tan_half_fov = std::tan(0.5 * vertical_fov_rad); // update-cpu.cpp:27
+    std::memcpy(c->bg, bg_color, sizeof(c->bg));
+    c->max_reflections = (int) max_reflections;
+
+    // ---- classify and repack --------------------------------------------------------------------
+    std::vector<double4> plane, sphere;
+    std::vector<float4> sphere_f, material(n_objects);
+    std::vector<double> quadric, cubic, coef_full(20 * n_objects);
+    std::vector<int> orig[4];
+    float center_max = 0.0f;
+    const char *obj_bytes = static_cast<const char *>(objects);
+    for (size_t i = 0; i < n_objects; i++) {
+        double k[20];
+        float refl, color[3];
+        std::memcpy(k, obj_bytes + RT_B200_OBJECT_BYTES * i, 160);
+        std::memcpy(&refl, obj_bytes + RT_B200_OBJECT_BYTES * i + 160, 4);
+        std::memcpy(color, obj_bytes + RT_B200_OBJECT_BYTES * i + 164, 12);
+        std::memcpy(&coef_full[20 * i], k, 160);
+        material[i] = make_float4(refl, color[0], color[1], color[2]);
+        rt::ObjClass cls = classify(k);
+        orig[cls].push_back((int) i);
+        switch (cls) {
+            case rt::CLS_PLANE:
+                plane.push_back(make_double4(k[rt::LX], k[rt::LY], k[rt::LZ], k[rt::CC]));
+                break;
+            case rt::CLS_SPHERE: {
+                sphere.push_back(make_double4(k[rt::LX], k[rt::LY], k[rt::LZ], k[rt::CC]));
+                // |p|^2 + l.p + c = 0  ->  centre -l/2, r^2 = |centre|^2 - c
+                double cx = -0.5 * k[rt::LX], cy = -0.5 * k[rt::LY], cz = -0.5 * k[rt::LZ];
+                double r2 = cx * cx + cy * cy + cz * cz - k[rt::CC];
+                sphere_f.push_back(make_float4((float) cx, (float) cy, (float) cz, (float) r2));
+                center_max = fmaxf(center_max, fmaxf(fabsf((float) cx), fmaxf(fabsf((float) cy), fabsf((float) cz))));
+                break;
+            }
+            case rt::CLS_QUADRIC:
+                for (int j = rt::X2; j <= rt::CC; j++) quadric.push_back(k[j]);
+                break;
+            case rt::CLS_CUBIC:
+                for (int j = 0; j < 20; j++) cubic.push_back(k[j]);
+                break;
+        }
+    }
+    std::vector<int> orig_index;
+    for (int cls = 0; cls < 4; cls++) {
+        c->class_counts[cls] = (uint32_t) orig[cls].size();
+        orig_index.insert(orig_index.end(), orig[cls].begin(), orig[cls].end());
+    }
+    std::vector<rt::LightDev> ldev(n_lights);
+    const char *light_bytes = static_cast<const char *>(lights);
+    for (size_t j = 0; j < n_lights; j++) {
+        const char *rec = light_bytes + RT_B200_LIGHT_BYTES * j;
+        double p[3];
+        float col[3];
+        std::memcpy(p, rec + 8, 24);
+        std::memcpy(col, rec + 32, 12);
+        ldev[j] = rt::LightDev{p[0], p[1], p[2], col[0], col[1], col[2], rec[0] != 0 ? 1 : 0};
+    }
+
+    int rc = RT_B200_OK;
+    auto up = [&](cudaError_t e, const char *what) {
+        if (e != cudaSuccess && rc == RT_B200_OK) rc = fail(RT_B200_ERR_CUDA, "upload %s: %s", what, cudaGetErrorString(e));
+    };
+    up(upload(plane, &c->d_plane), "planes");
+    up(upload(sphere, &c->d_sphere), "spheres");
+    up(upload(sphere_f, &c->d_sphere_f), "sphere filter");
+    up(upload(quadric, &c->d_quadric), "quadrics");
+    up(upload(cubic, &c->d_cubic), "cubics");
+    up(upload(coef_full, &c->d_coef_full), "coefficients");
+    up(upload(material, &c->d_material), "materials");
+    up(upload(orig_index, &c->d_orig), "index map");
+    up(upload(ldev, &c->d_lights), "lights");
+    up(cudaMalloc((void **) &c->d_counters, sizeof(unsigned long long) * rt::CNT_COUNT), "counters");
+    up(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "stream");
+    up(cudaEventCreate(&c->ev_start), "event");
+    up(cudaEventCreate(&c->ev_render), "event");
+    up(cudaEventCreate(&c->ev_end), "event");
+    if (rc != RT_B200_OK) {
+        rt_b200_destroy(c);
+        return rc;
+    }
+    cudaMemset(c->d_counters, 0, sizeof(unsigned long long) * rt::CNT_COUNT);
+
+    rt::SceneView &v = c->view;
+    v.n_plane = (int) plane.size();
+    v.n_sphere = (int) sphere.size();
+    v.n_quadric = (int) quadric.size() / 10;
+    v.n_cubic = (int) cubic.size() / 20;
+    v.n_objects = (int) n_objects;
+    v.n_lights = (int) n_lights;
+    v.plane = c->d_plane;
+    v.sphere = c->d_sphere;
+    v.sphere_f = c->d_sphere_f;
+    v.quadric = c->d_quadric;
+    v.cubic = c->d_cubic;
+    v.orig_index = c->d_orig;
+    v.coef_full = c->d_coef_full;
+    v.material = c->d_material;
+    v.lights = c->d_lights;
+    v.sphere_center_max = center_max;
+
+    rc = ensure_buffers(c);
+    if (rc != RT_B200_OK) {
+        rt_b200_destroy(c);
+        return rc;
+    }
+    *ctx_out = c;
+    return RT_B200_OK;
+}
+
+int rt_b200_update(rt_b200_ctx *c, const double camera_matrix[16], float *elapsed_ms)
+{
+    if (!c || !camera_matrix) return fail(RT_B200_ERR_ARG, "null argument");
+    CUDA_TRY(cudaSetDevice(c->device));
+    int rc = ensure_buffers(c);
+    if (rc != RT_B200_OK) return rc;
+
+    rt::FrameParams f;
+    std::memcpy(f.m, camera_matrix, sizeof(f.m));
+    // origin = M * (0,0,0,1) in GLM's association: (m0*0 + m1*0) + (m2*0 + m3*1), update-cpu.cpp:123
+    for (int r = 0; r < 3; r++)
+        f.origin[r] = (f.m[r] * 0.0 + f.m[4 + r] * 0.0) + (f.m[8 + r] * 0.0 + f.m[12 + r] * 1.0);
+    f.aspect = c->aspect;
+    f.tan_half_fov = c->tan_half_fov;
+    std::memcpy(f.bg, c->bg, sizeof(f.bg));
+    f.max_reflections = c->max_reflections;
+    f.width = c->width;
+    f.height = c->height;
+    f.strip_rows = (c->world == 1) ? c->height : c->strip_rows;
+    f.rank = c->rank;
+    f.world = c->world;
+    f.local_rows = c->local_rows;
+    f.out = c->d_local;
+    f.counters = c->count ? c->d_counters : nullptr;
+
+    if (c->count) CUDA_TRY(cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long) * rt::CNT_COUNT, c->stream));
+    CUDA_TRY(cudaEventRecord(c->ev_start, c->stream));
+    CUDA_TRY(rt::launch_render_exact(c->view, f, c->stream));
+    CUDA_TRY(cudaEventRecord(c->ev_render, c->stream));
+    if (c->world > 1 && c->comm) {
+        const size_t bytes = sizeof(uchar4) * (size_t) c->width * c->local_rows;
+        NCCL_TRY(g_nccl.AllGather(c->d_local, c->d_gathered, bytes, ncclUint8, c->comm, c->stream));
+        CUDA_TRY(rt::launch_unpack_strips(c->d_gathered, c->d_frame, c->width, c->height, c->strip_rows, c->world,
+                                          c->local_rows, c->stream));
+    }
+    CUDA_TRY(cudaEventRecord(c->ev_end, c->stream));
+    CUDA_TRY(cudaEventSynchronize(c->ev_end));
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaEventElapsedTime(&c->ms_render, c->ev_start, c->ev_render));
+    CUDA_TRY(cudaEventElapsedTime(&c->ms_gather, c->ev_render, c->ev_end));
+    c->rendered = true;
+    if (elapsed_ms) *elapsed_ms = c->ms_render + c->ms_gather;
+    return RT_B200_OK;
+}
+
+int rt_b200_gather(rt_b200_ctx *c, void *host_rgba8, size_t host_bytes, const void **device_rgba8)
+{
+    if (!c) return fail(RT_B200_ERR_ARG, "null context");
+    if (!c->rendered) return fail(RT_B200_ERR_STATE, "rt_b200_gather before the first rt_b200_update");
+    CUDA_TRY(cudaSetDevice(c->device));
+    const size_t frame_bytes = sizeof(uchar4) * (size_t) c->width * c->height;
+    const uchar4 *frame = c->d_local;
+    if (c->world > 1) {
+        frame = c->d_frame;
+        if (!c->comm) {
+            // no communicator: expose this rank's rows in place, the others stay zero
+            CUDA_TRY(cudaMemsetAsync(c->d_gathered, 0, sizeof(uchar4) * (size_t) c->width * c->local_rows * c->world,
+                                     c->stream));
+            CUDA_TRY(cudaMemcpyAsync(c->d_gathered + (size_t) c->rank * c->local_rows * c->width, c->d_local,
+                                     sizeof(uchar4) * (size_t) c->width * c->local_rows, cudaMemcpyDeviceToDevice,
+                                     c->stream));
+            CUDA_TRY(rt::launch_unpack_strips(c->d_gathered, c->d_frame, c->width, c->height, c->strip_rows, c->world,
+                                              c->local_rows, c->stream));
+            CUDA_TRY(cudaStreamSynchronize(c->stream));
+        }
+    }
+    if (host_rgba8) {
+        if (host_bytes < frame_bytes)
+            return fail(RT_B200_ERR_ARG, "host buffer holds %zu bytes, frame needs %zu", host_bytes, frame_bytes);
+        CUDA_TRY(cudaMemcpyAsync(host_rgba8, frame, frame_bytes, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+    }
+    if (device_rgba8) *device_rgba8 = frame;
+    return RT_B200_OK;
+}
+
+int rt_b200_destroy(rt_b200_ctx *c)
+{
+    if (!c) return RT_B200_OK;
+    cudaSetDevice(c->device);
+    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    free_buffers(c);
+    cudaFree(c->d_plane);
+    cudaFree(c->d_sphere);
+    cudaFree(c->d_sphere_f);
+    cudaFree(c->d_quadric);
+    cudaFree(c->d_cubic);
+    cudaFree(c->d_coef_full);
+    cudaFree(c->d_material);
+    cudaFree(c->d_orig);
+    cudaFree(c->d_lights);
+    cudaFree(c->d_counters);
+    if (c->ev_start) cudaEventDestroy(c->ev_start);
+    if (c->ev_render) cudaEventDestroy(c->ev_render);
+    if (c->ev_end) cudaEventDestroy(c->ev_end);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return RT_B200_OK;
+}
+
+int rt_b200_comm_unique_id(void *id_out)
+{
+    if (!id_out) return fail(RT_B200_ERR_ARG, "id_out is null");
+    int rc = load_nccl();
+    if (rc != RT_B200_OK) return rc;
+    static_assert(sizeof(ncclUniqueId) == RT_B200_UNIQUE_ID_BYTES, "ncclUniqueId size");
+    ncclUniqueId id;
+    NCCL_TRY(g_nccl.GetUniqueId(&id));
+    std::memcpy(id_out, &id, sizeof(id));
+    return RT_B200_OK;
+}
+
+int rt_b200_comm_init(rt_b200_ctx *c, const void *id_bytes)
+{
+    if (!c || !id_bytes) return fail(RT_B200_ERR_ARG, "null argument");
+    if (c->world < 2) return fail(RT_B200_ERR_ARG, "communicator needs world_size > 1");
+    int rc = load_nccl();
+    if (rc != RT_B200_OK) return rc;
+    CUDA_TRY(cudaSetDevice(c->device));
+    ncclUniqueId id;
+    std::memcpy(&id, id_bytes, sizeof(id));
+    NCCL_TRY(g_nccl.CommInitRank(&c->comm, c->world, id, c->rank));
+    return RT_B200_OK;
+}
+
+int rt_b200_get_counters(rt_b200_ctx *c, rt_b200_counters *out)
+{
+    if (!c || !out) return fail(RT_B200_ERR_ARG, "null argument");
+    static_assert(sizeof(rt_b200_counters) == sizeof(unsigned long long) * rt::CNT_COUNT, "counter layout");
+    CUDA_TRY(cudaSetDevice(c->device));
+    CUDA_TRY(cudaMemcpy(out, c->d_counters, sizeof(*out), cudaMemcpyDeviceToHost));
+    return RT_B200_OK;
+}
+
+int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
+{
+    if (!c || !name) return fail(RT_B200_ERR_ARG, "null argument");
+    if (!std::strcmp(name, "kernel")) {
+        if (value < 0 || value > 1) return fail(RT_B200_ERR_ARG, "kernel must be 0 or 1");
+        c->kernel_kind = (int) value;
+    }
+    else if (!std::strcmp(name, "strip_rows")) {
+        if (value < 1 || value > 4096) return fail(RT_B200_ERR_ARG, "strip_rows out of range");
+        if (c->strip_rows != (int) value) {
+            c->strip_rows = (int) value;
+            c->buffers_dirty = true;
+        }
+    }
+    else if (!std::strcmp(name, "count")) {
+        c->count = value != 0;
+    }
+    else {
+        return fail(RT_B200_ERR_ARG, "unknown option '%s'", name);
+    }
+    return RT_B200_OK;
+}
+
+int rt_b200_get_timing(rt_b200_ctx *c, float out_ms[2])
+{
+    if (!c || !out_ms) return fail(RT_B200_ERR_ARG, "null argument");
+    out_ms[0] = c->ms_render;
+    out_ms[1] = c->ms_gather;
+    return RT_B200_OK;
+}
+
+int rt_b200_get_class_counts(rt_b200_ctx *c, uint32_t out[4])
+{
+    if (!c || !out) return fail(RT_B200_ERR_ARG, "null argument");
+    std::memcpy(out, c->class_counts, sizeof(c->class_counts));
+    return RT_B200_OK;
+}
+
+} // extern "C"

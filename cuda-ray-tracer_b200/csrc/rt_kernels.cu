@@ -1,0 +1,116 @@
+// rt_kernels.cu — sm_100a kernels of the per-pixel frame update.
+//
+// Replaces the reference's single update_kernel (src/update-cuda.cu:104-158) — not a port of it: the scene is
+// class-sorted SoA (rt_scene.h), the arithmetic is the reference CPU path's exact FP64 order (rt_math.cuh),
+// the frame is a plain RGBA8 device buffer instead of a GL surface, and rows are strip-interleaved over ranks.
+#include "rt_kernels.h"
+#include "rt_trace.cuh"
+
+namespace rt {
+
+// ---------------------------------------------------------------------------------------------------
+// Exact kernel: 256 threads = a 32x8 pixel tile, each warp an 8x4 sub-tile (coherent rays, and each
+// warp writes four fully used 32-byte sectors).
+// ---------------------------------------------------------------------------------------------------
+constexpr int TILE_W = 32;
+constexpr int TILE_H = 8;
+
+__global__ void __launch_bounds__(TILE_W *TILE_H)
+render_exact_kernel(const __grid_constant__ SceneView sc, const __grid_constant__ FrameParams f)
+{
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int x = blockIdx.x * TILE_W + (warp & 3) * 8 + (lane & 7);
+    const int lrow = blockIdx.y * TILE_H + (warp >> 2) * 4 + (lane >> 3);
+    const int y = local_to_image_row(lrow, f.strip_rows, f.rank, f.world);
+    const bool live = x < f.width && lrow < f.local_rows && y < f.height;
+
+    Tally tl;
+    tl.clear();
+    if (live) {
+        const d3 origin = d3{f.origin[0], f.origin[1], f.origin[2]};
+        d3 dir = primary_dir(f, origin, x, y);
+        tl.n[CNT_PRIMARY]++;
+
+        float3 hit_color;
+        d3 p, n;
+        int idx = trace_and_shade_exact(sc, origin, dir, hit_color, p, n, tl);
+        float3 out;
+        if (idx < 0) {
+            out = make_float3(f.bg[0], f.bg[1], f.bg[2]);
+        }
+        else {
+            // reflection loop, update-cpu.cpp:97-117; blending uses the cumulative ratio
+            out = hit_color;
+            float ratio = 1.0f;
+            int bounces = 0;
+            float refl = __ldg(&sc.material[idx]).x;
+            while (refl > RT_EPS) {
+                ratio *= refl;
+                float3 blend = make_float3(f.bg[0], f.bg[1], f.bg[2]);
+                bool stop = true;
+                if (bounces != f.max_reflections) {
+                    bounces++;
+                    d3 rd = reflect(dir, n);
+                    d3 ro = d3{p.x + RT_SHADOW_BIAS * n.x, p.y + RT_SHADOW_BIAS * n.y, p.z + RT_SHADOW_BIAS * n.z};
+                    dir = rd;
+                    tl.n[CNT_REFLECTION]++;
+                    idx = trace_and_shade_exact(sc, ro, dir, hit_color, p, n, tl);
+                    if (idx >= 0) {
+                        blend = hit_color;
+                        stop = false;
+                        refl = __ldg(&sc.material[idx]).x;
+                    }
+                }
+                out.x = (1.0f - ratio) * out.x + ratio * blend.x;
+                out.y = (1.0f - ratio) * out.y + ratio * blend.y;
+                out.z = (1.0f - ratio) * out.z + ratio * blend.z;
+                if (stop) break;
+            }
+        }
+        f.out[(size_t) lrow * f.width + x] = pack_rgba8(out.x, out.y, out.z);
+    }
+    else if (x < f.width && lrow < f.local_rows) {
+        f.out[(size_t) lrow * f.width + x] = make_uchar4(0, 0, 0, 0);   // padding row past the image
+    }
+    flush_tally(tl, f.counters);
+}
+
+cudaError_t launch_render_exact(const SceneView &scene, const FrameParams &frame, cudaStream_t stream)
+{
+    dim3 block(TILE_W * TILE_H);
+    dim3 grid((frame.width + TILE_W - 1) / TILE_W, (frame.local_rows + TILE_H - 1) / TILE_H);
+    render_exact_kernel<<<grid, block, 0, stream>>>(scene, frame);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Strip un-interleave after the all-gather.  16 bytes (4 pixels) per thread when the width allows.
+// ---------------------------------------------------------------------------------------------------
+__global__ void unpack_strips_kernel(const uchar4 *__restrict__ gathered, uchar4 *__restrict__ frame, int width,
+                                     int height, int strip_rows, int world, int local_rows)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y;
+    if (x >= width || y >= height) return;
+    const int strip = y / strip_rows;
+    const int owner = strip % world;
+    const int lrow = (strip / world) * strip_rows + (y - strip * strip_rows);
+    frame[(size_t) y * width + x] = gathered[((size_t) owner * local_rows + lrow) * width + x];
+}
+
+cudaError_t launch_unpack_strips(const uchar4 *gathered, uchar4 *frame, int width, int height, int strip_rows,
+                                 int world, int local_rows, cudaStream_t stream)
+{
+    dim3 block(256);
+    dim3 grid((width + 255) / 256, height);
+    unpack_strips_kernel<<<grid, block, 0, stream>>>(gathered, frame, width, height, strip_rows, world, local_rows);
+    return cudaGetLastError();
+}
+
+int render_launch_count(int kernel_kind)
+{
+    (void) kernel_kind;
+    return 1;
+}
+
+} // namespace rt

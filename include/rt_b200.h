@@ -1,0 +1,119 @@
+/* rt_b200.h — C ABI of the B200-native frame-update library (librt_b200.so).
+ *
+ * This is the drop-in boundary for the reference's back-end call surface,
+ * /root/reference/include/update.h:6-8:
+ *
+ *     void  init_update(unsigned int texture, const Scene& scene);     -> rt_b200_upload_scene
+ *     float update(const glm::dmat4& camera_matrix);                   -> rt_b200_update
+ *     void  cleanup_update();                                          -> rt_b200_destroy
+ *
+ * plus rt_b200_gather, which replaces the GL texture the reference writes into
+ * (src/update-cuda.cu:59,166-174) as the result sink: there is no graphics stack on the target box, so
+ * the frame lives in a plain device buffer and is copied to the caller on request.
+ *
+ * Conventions: plain C types only; every call returns an int status (RT_B200_OK == 0) instead of the
+ * reference's print-and-exit(1) (include/helper_cuda_opengl.h:13-44); rt_b200_last_error() describes
+ * the last failure on the calling thread; state lives in an opaque context instead of file-scope
+ * globals (src/update-cuda.cu:15-27); one caller thread per context; every call is synchronous.
+ * There is no CPU fallback: without a CUDA device every compute entry point fails with
+ * RT_B200_ERR_CUDA.
+ */
+#ifndef RT_B200_H
+#define RT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_B200_OK 0
+#define RT_B200_ERR_ARG 1      /* bad argument (null pointer, zero size, unknown option, small buffer) */
+#define RT_B200_ERR_CUDA 2     /* a CUDA runtime call failed (including: no device)                  */
+#define RT_B200_ERR_NCCL 3     /* NCCL missing or an NCCL call failed                                */
+#define RT_B200_ERR_STATE 4    /* call out of order (e.g. gather before the first update)            */
+
+#define RT_B200_OBJECT_BYTES 176 /* sizeof(Object),      include/scene.h:8-15  */
+#define RT_B200_LIGHT_BYTES 48   /* sizeof(LightSource), include/light.h:6-13  */
+#define RT_B200_UNIQUE_ID_BYTES 128
+
+typedef struct rt_b200_ctx rt_b200_ctx;
+
+/* Work actually executed by the last rt_b200_update on THIS rank (64-bit, exact).
+ * rays = primary + reflection + shadow, the reference's ray definition. */
+typedef struct {
+    uint64_t primary_rays;    /* one per pixel rendered by this rank                                   */
+    uint64_t reflection_rays; /* bounce rays cast (update-cpu.cpp:104-111)                             */
+    uint64_t shadow_rays;     /* one per light per hit (update-cpu.cpp:62-64)                          */
+    uint64_t hits;            /* nearest-hit searches that found an object                             */
+    uint64_t lit;             /* unshadowed light evaluations (surface_color calls)                    */
+    uint64_t tests_plane;     /* (ray, object) tests this kernel performed, by structural class ...    */
+    uint64_t tests_sphere;
+    uint64_t tests_quadric;
+    uint64_t tests_cubic;
+    uint64_t fp64_confirms;   /* sphere tests that fell through the FP32 filter to the exact FP64 test */
+} rt_b200_counters;
+
+/* == init_update(texture, scene), update.h:6.
+ * Copies everything it needs; the caller keeps ownership of all inputs.
+ *   px_width, px_height, vertical_fov_rad, bg_color, max_reflections : Scene scalars, include/scene.h:19-22
+ *       (vertical_fov in RADIANS, as Scene stores it after scene.cpp:20)
+ *   objects : n_objects records in the reference's Object layout (176 B: 20 doubles in SurfaceCoefs order
+ *             x3,y3,z3,x2y,xy2,x2z,xz2,y2z,yz2,xyz,x2,y2,z2,xy,xz,yz,x,y,z,c; float reflection_ratio @160;
+ *             float color[3] @164) — i.e. &scene.objects[0]
+ *   lights  : n_lights records in the reference's LightSource layout (48 B: bool is_spherical @0,
+ *             double p[3] @8, float light_color[3] @32) — i.e. &scene.lights[0]
+ *   device  : CUDA device ordinal this context renders on
+ *   rank, world_size : this context renders the image strips s with s % world_size == rank
+ *             (1-GPU use: rank 0, world_size 1).  For world_size > 1 call rt_b200_comm_init next. */
+int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_height, double vertical_fov_rad,
+                         const float bg_color[3], uint32_t max_reflections, const void *objects, size_t n_objects,
+                         const void *lights, size_t n_lights, int device, int rank, int world_size);
+
+/* == update(camera_matrix), update.h:7.
+ * camera_matrix: 16 doubles, GLM column-major (&m[0][0]).  Renders this rank's strips and, when a
+ * communicator is attached, all-gathers the strips so that every rank holds the full frame.
+ * *elapsed_ms (may be NULL) = CUDA-event time from the first launch to the end of the gather, the value
+ * the reference's update() returns (src/update-cuda.cu:178-189). */
+int rt_b200_update(rt_b200_ctx *ctx, const double camera_matrix[16], float *elapsed_ms);
+
+/* Result sink (replaces the GL texture).  Frame = px_width*px_height RGBA8 pixels, row 0 = bottom row of the
+ * picture (as in the reference: ray-tracer.cpp:12-17, update-cpu.cpp:85-87), alpha = 255.
+ *   host_rgba8 != NULL : copy the frame into it (host_bytes must be >= px_width*px_height*4)
+ *   device_rgba8 != NULL : receives the device pointer of the assembled frame on this rank's GPU
+ * With world_size > 1 and no communicator attached only this rank's rows are valid. */
+int rt_b200_gather(rt_b200_ctx *ctx, void *host_rgba8, size_t host_bytes, const void **device_rgba8);
+
+/* == cleanup_update(), update.h:8. */
+int rt_b200_destroy(rt_b200_ctx *ctx);
+
+const char *rt_b200_last_error(void);
+
+/* ---- multi-GPU: one process (or thread) per GPU, NCCL over NVLink --------------------------------
+ * Rank 0 obtains an id, the host distributes the 128 bytes to all ranks by any means (the Python host
+ * uses torch.distributed), then every rank attaches its context.  libnccl.so.2 is loaded on first use. */
+int rt_b200_comm_unique_id(void *id_out /* RT_B200_UNIQUE_ID_BYTES */);
+int rt_b200_comm_init(rt_b200_ctx *ctx, const void *id /* RT_B200_UNIQUE_ID_BYTES */);
+
+/* ---- introspection and tuning -------------------------------------------------------------------- */
+int rt_b200_get_counters(rt_b200_ctx *ctx, rt_b200_counters *out);
+
+/* Options: "kernel"     0 = exact FP64 kernel (thread per pixel), 1 = wavefront kernel (default)
+ *          "strip_rows" image rows per strip of the multi-GPU interleave (default 8)
+ *          "count"      1 = maintain rt_b200_counters (default), 0 = skip them                       */
+int rt_b200_set_option(rt_b200_ctx *ctx, const char *name, int64_t value);
+
+/* Split timing of the last update, milliseconds: [0] render kernels, [1] gather (all-gather + unpack). */
+int rt_b200_get_timing(rt_b200_ctx *ctx, float out_ms[2]);
+
+/* Structural class counts of the uploaded scene: planes, spheres, quadrics, cubics. */
+int rt_b200_get_class_counts(rt_b200_ctx *ctx, uint32_t out[4]);
+
+/* Library build tag, e.g. "rt_b200 0.1 sm_100a". */
+const char *rt_b200_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,19 @@
+"""Import the package directory `cuda-ray-tracer_b200/` (not a valid identifier) as `cuda_ray_tracer_b200`."""
+import importlib.util
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG_DIR = os.path.join(ROOT, "cuda-ray-tracer_b200")
+PKG_NAME = "cuda_ray_tracer_b200"
+
+
+def load_package():
+    if PKG_NAME in sys.modules:
+        return sys.modules[PKG_NAME]
+    spec = importlib.util.spec_from_file_location(PKG_NAME, os.path.join(PKG_DIR, "__init__.py"),
+                                                  submodule_search_locations=[PKG_DIR])
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[PKG_NAME] = mod
+    spec.loader.exec_module(mod)
+    return mod
