@@ -1,0 +1,387 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200-native frame update (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload bundled4k|synthetic]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+
+Workload `bundled4k` (default, the configuration the metric is quoted on): one STEP = one 3840x2160,
+4-bounce frame of each of the eight bundled scenes (the reference's initial camera pose), i.e. eight
+rt_b200_update calls.  `value` = rays cast per second over the whole job (primary + reflection + shadow
+rays), inputs resident on the device.  `e2e` = the same through the C ABI with HOST
+buffers: camera matrix from host memory in, finished RGBA8 frame copied to pinned host memory out, every
+frame.  With N > 1 ranks (one process per GPU) every rank renders its interleaved strips of every frame
+and the strips are all-gathered over NCCL inside rt_b200_update; time is the max over ranks.
+
+`--impl reference` times the reference's own CPU implementation (oracle/_ref = update-cpu.cpp compiled
+unmodified, else the C restatement) on the host cores, on a bounded row sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tools")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+BUNDLED = ["20spheres", "quadratic", "cubic", "cayley", "clebsch", "dingdong", "monkey_saddle", "reflection_test"]
+WIDTH, HEIGHT, BOUNCES = 3840, 2160, 4
+METRIC, UNIT = "Mrays/s", "Mrays/s"
+
+# Canonical algorithmic flops: per (ray, object) test by structural class, per primary ray,
+# per hit, per unshadowed light evaluation, per bounce.
+FLOPS = {"tests_plane": 13, "tests_sphere": 38, "tests_quadric": 81, "tests_cubic": 320,
+         "primary_rays": 50, "hits": 70, "lit": 35, "reflection_rays": 12}
+
+
+def canonical_flops(c: dict) -> float:
+    return float(sum(c[k] * w for k, w in FLOPS.items()))
+
+
+def load_peaks() -> dict:
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        p["_source"] = "measured"
+        return p
+    return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0, "_source": "fallback"}
+
+
+def fp32_peak_tflops(n_sms: int, sm_mhz: float) -> float:
+    """FP32 SIMT peak: SMs x 128 lanes x 2 flop (FMA) x clock."""
+    return n_sms * 128 * 2 * sm_mhz * 1e6 / 1e12
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.lines:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        # samples under load = the upper half (the sampler also sees idle gaps between steps)
+        sm_sorted = sorted(sm)
+        load = sm_sorted[len(sm_sorted) // 2:] if sm_sorted else []
+        return {"sm_mhz": float(np.median(load)) if load else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    return rank, local, world
+
+
+def build_workload(pkg, name: str):
+    """Returns [(label, Scene)] and a description."""
+    if name == "bundled4k":
+        scenes = []
+        for s in BUNDLED:
+            sc = pkg.load_from_file(os.path.join(ROOT, "scenes", s + ".yml")).with_overrides(
+                width=WIDTH, height=HEIGHT, max_reflections=BOUNCES)
+            scenes.append((s, sc))
+        return scenes, "8 bundled scenes @ {}x{}, max_reflections {}, initial camera".format(WIDTH, HEIGHT, BOUNCES)
+    if name == "synthetic":
+        from cuda_ray_tracer_b200 import synth
+        sc = synth.synthetic_scene()
+        return [("synth_4096s_64c_16l", sc)], "synthetic 4096 spheres + 64 cubics + 16 point lights @ 7680x4320, 4 bounces"
+    raise SystemExit("unknown workload " + name)
+
+
+# --------------------------------------------------------------------------------------------------
+def run_reference(args):
+    """The reference's own CPU implementation on the host cores, bounded sample of the same workload."""
+    rank, _, world = dist_env()
+    if rank != 0:
+        return
+    from loader import load_package
+    pkg = load_package()
+    from cuda_ray_tracer_b200 import camera
+    from oracle import oracle_py
+    oracle_py.build()
+    scenes, desc = build_workload(pkg, args.workload)
+    cores = os.cpu_count() or 1
+    kind = "reference" if oracle_py.have_ref() else "port"
+    ystep = args.ref_row_step
+    m = camera.TEST_POSES["initial"]
+    # ray census of the sampled rows (untimed, via the counting restatement)
+    rays_sample = 0
+    for _, sc in scenes:
+        _, _, cnt = oracle_py.PortOracle(sc).render_rows(m, 0, sc.px_height, ystep, threads=cores, count=True)
+        rays_sample += cnt["primary_rays"] + cnt["reflection_rays"] + cnt["shadow_rays"]
+
+    def step() -> float:
+        """Seconds inside the pixel loops only — the reference's own timing convention (update-cpu.cpp:124-138);
+        its init_update (a 100 MB float buffer fill per 4K scene) is left out."""
+        ms_total = 0.0
+        for _, sc in scenes:
+            if kind == "reference":
+                ms_total += oracle_py.RefCpu(sc).render_rows(m, 0, sc.px_height, ystep, threads=cores)[1]
+            else:
+                ms_total += oracle_py.PortOracle(sc).render_rows(m, 0, sc.px_height, ystep, threads=cores)[1]
+        return ms_total / 1e3
+
+    for _ in range(args.warmup):
+        step()
+    dt = sum(step() for _ in range(args.steps)) / args.steps
+    value = rays_sample / dt / 1e6
+    sample = "every {}th image row of each frame ({} rows per 2160), {} host threads".format(
+        ystep, len(range(0, HEIGHT, ystep)), cores)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, "description": desc, "sampled": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from loader import load_package
+    pkg = load_package()
+    from cuda_ray_tracer_b200 import binding, camera
+
+    rank, local, world = dist_env()
+    if world != args.gpus and world != 1:
+        raise SystemExit("--gpus {} but WORLD_SIZE {}".format(args.gpus, world))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the B200 path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    binding.load_library()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    scenes, desc = build_workload(pkg, args.workload)
+    m = np.ascontiguousarray(camera.TEST_POSES["initial"])
+    renderers = []
+    for label, sc in scenes:
+        r = binding.Renderer(sc, device=local, rank=rank, world_size=world)
+        r.set_option("kernel", args.kernel)
+        if world > 1:
+            r.set_option("strip_rows", args.strip_rows)
+            ident = [binding.comm_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(ident, src=0)
+            r.comm_init(ident[0])
+        renderers.append((label, sc, r))
+
+    frame_bytes = max(sc.px_width * sc.px_height * 4 for _, sc in scenes)
+    host_frame = torch.empty(frame_bytes, dtype=torch.uint8).pin_memory()
+    host_cam = torch.from_numpy(m.copy()).pin_memory()
+
+    def step_device():
+        for _, _, r in renderers:
+            r.update(m)
+
+    def step_e2e():
+        for _, sc, r in renderers:
+            r.update(host_cam.numpy())                                  # H2D: the camera matrix (kernel params)
+            r.gather_into(host_frame.data_ptr(), sc.px_width * sc.px_height * 4)   # D2H: the finished frame
+
+    # ---- device-resident timing ------------------------------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    sampler = ClockSampler(local)
+    per_scene = {label: {"render_ms": 0.0, "gather_ms": 0.0} for label, _, _ in renderers}
+    barrier()
+    if rank == 0:
+        sampler.start()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        for label, _, r in renderers:
+            r.update(m)
+            t = r.timing()
+            per_scene[label]["render_ms"] += t["render_ms"]
+            per_scene[label]["gather_ms"] += t["gather_ms"]
+    barrier()
+    dt = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- end-to-end timing (host buffers) ----------------------------------------------------------
+    for _ in range(2):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    barrier()
+    dt_e2e = time.perf_counter() - t0
+
+    # ---- census: rays and canonical flops of one step, summed over ranks ----------------------------
+    local_counts = {}
+    for label, _, r in renderers:
+        local_counts[label] = r.counters()
+    keys = list(binding.COUNTER_FIELDS)
+    mat = torch.tensor([[local_counts[label][k] for k in keys] for label, _, _ in renderers], dtype=torch.int64,
+                       device="cuda")
+    times = torch.tensor([dt, dt_e2e], dtype=torch.float64, device="cuda")
+    kern = torch.tensor([[per_scene[label]["render_ms"], per_scene[label]["gather_ms"]] for label, _, _ in renderers],
+                        dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(mat, op=dist.ReduceOp.SUM)
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+        dist.all_reduce(kern, op=dist.ReduceOp.MAX)
+    mat, times, kern = mat.cpu().numpy(), times.cpu().numpy(), kern.cpu().numpy() / args.steps
+
+    if rank == 0:
+        peaks = load_peaks()
+        props = torch.cuda.get_device_properties(local)
+        n_sms = props.multi_processor_count
+        fp32_peak = fp32_peak_tflops(n_sms, float(peaks.get("sm_max_mhz", 1965.0)))
+        totals = {k: int(mat[:, i].sum()) for i, k in enumerate(keys)}
+        rays_step = totals["primary_rays"] + totals["reflection_rays"] + totals["shadow_rays"]
+        flops_step = canonical_flops(totals)
+        ms_step = times[0] / args.steps * 1e3
+        ms_e2e = times[1] / args.steps * 1e3
+        render_ms_sum = float(kern[:, 0].sum())          # per step, max over ranks per scene
+        scenes_out = {}
+        for i, (label, sc, _) in enumerate(renderers):
+            c = {k: int(mat[i, j]) for j, k in enumerate(keys)}
+            rays = c["primary_rays"] + c["reflection_rays"] + c["shadow_rays"]
+            fl = canonical_flops(c)
+            rms = float(kern[i, 0])
+            scenes_out[label] = {
+                "ms_frame_kernel": rms, "ms_gather": float(kern[i, 1]), "mrays_s_kernel": rays / rms / 1e3,
+                "rays": rays, "gflop": fl / 1e9, "tflops": fl / rms / 1e9, "fp32_frac": fl / rms / 1e9 / (fp32_peak * world),
+                "fb_write_gbs": sc.px_width * sc.px_height * 4 / rms / 1e6,
+            }
+        achieved = flops_step / render_ms_sum / 1e9 / world    # TFLOP/s per GPU over the render kernels
+        launches = args.steps * len(renderers) * (1 + (1 if world > 1 else 0))
+        line = {
+            "metric": METRIC, "value": rays_step / ms_step / 1e3, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": args.workload, "description": desc, "frames_per_step": len(renderers),
+                       "rays_per_step": rays_step, "kernel": args.kernel,
+                       "parallelism": "strips{}x{}rows".format(world, args.strip_rows) if world > 1 else "1gpu",
+                       "l2": "outputs ({} MB per step) exceed the 126 MB L2; the scene (KBs) is cache-resident by design"
+                             .format(len(renderers) * frame_bytes // 1000000)},
+            "e2e": {"value": rays_step / ms_e2e / 1e3, "unit": UNIT, "ms_per_step": ms_e2e,
+                    "h2d_bytes_per_step": len(renderers) * 128,
+                    "d2h_bytes_per_step": int(sum(sc.px_width * sc.px_height * 4 for _, sc, _ in renderers))},
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s",
+                         "frac": achieved / fp32_peak, "traffic": None,
+                         "peak_source": "148 SMs x 128 lanes x 2 x sm_max_mhz of MEASURED_PEAKS.json ({})".format(peaks["_source"]),
+                         "algorithmic_gflop_per_step": flops_step / 1e9, "kernel_ms_per_step": render_ms_sum,
+                         "note": "canonical flops of SURVEY.md §8d over the render kernels' CUDA-event time; "
+                                 "the path is compute-bound (not hbm/tensor)",
+                         "hbm": {"achieved": len(renderers) * frame_bytes / render_ms_sum / 1e6, "peak": peaks["hbm_gbs"],
+                                 "unit": "GB/s", "what": "framebuffer write only"}},
+            "per_scene": scenes_out,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(pkg, scenes, args)
+        print(json.dumps(line), flush=True)
+
+    for _, _, r in renderers:
+        r.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_baseline(pkg, scenes, args) -> dict:
+    """The reference CPU path on this box's host cores, bounded row sample (about 10-30 s of CPU work)."""
+    from cuda_ray_tracer_b200 import camera
+    from oracle import oracle_py
+    oracle_py.build()
+    cores = os.cpu_count() or 1
+    kind = "reference" if oracle_py.have_ref() else "port"
+    m = camera.TEST_POSES["initial"]
+    ystep = args.ref_row_step
+    rays, secs = 0, 0.0
+    for _, sc in scenes:
+        _, _, cnt = oracle_py.PortOracle(sc).render_rows(m, 0, sc.px_height, ystep, threads=cores, count=True)
+        rays += cnt["primary_rays"] + cnt["reflection_rays"] + cnt["shadow_rays"]
+        if kind == "reference":
+            _, ms = oracle_py.RefCpu(sc).render_rows(m, 0, sc.px_height, ystep, threads=cores)
+        else:
+            _, ms = oracle_py.PortOracle(sc).render_rows(m, 0, sc.px_height, ystep, threads=cores)
+        secs += ms / 1e3
+    return {"value": rays / secs / 1e6, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": "every {}th image row of each frame of the workload, {} host threads, {:.1f} s".format(ystep, cores, secs)}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="bundled4k", choices=["bundled4k", "synthetic"])
+    ap.add_argument("--kernel", type=int, default=1)
+    ap.add_argument("--strip-rows", type=int, default=8)
+    ap.add_argument("--ref-row-step", type=int, default=8)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -26,7 +26,7 @@ COUNTER_FIELDS = ("primary_rays", "reflection_rays", "shadow_rays", "hits", "lit
 # every symbol include/rt_b200.h declares
 EXPORTS = ("rt_b200_upload_scene", "rt_b200_update", "rt_b200_gather", "rt_b200_destroy", "rt_b200_last_error",
            "rt_b200_comm_unique_id", "rt_b200_comm_init", "rt_b200_get_counters", "rt_b200_set_option",
-           "rt_b200_get_timing", "rt_b200_get_class_counts", "rt_b200_version")
+           "rt_b200_get_timing", "rt_b200_get_class_counts", "rt_b200_strip_layout", "rt_b200_version")
 
 UNIQUE_ID_BYTES = 128
 
@@ -64,6 +64,7 @@ def load_library():
     L.rt_b200_get_timing.argtypes = [vp, C.POINTER(C.c_float * 2)]
     L.rt_b200_get_class_counts.argtypes = [vp, C.POINTER(C.c_uint32 * 4)]
     L.rt_b200_version.restype = C.c_char_p
+    L.rt_b200_strip_layout.argtypes = [C.c_uint32, C.c_uint32, C.c_int, C.c_int, vp, C.c_size_t, C.POINTER(C.c_uint32)]
     _lib = L
     return L
 
@@ -75,6 +76,16 @@ def _check(rc: int):
 
 def _dp(a):
     return a.ctypes.data_as(C.c_void_p)
+
+
+def strip_layout(height: int, strip_rows: int, rank: int, world_size: int) -> np.ndarray:
+    """Image row held by each packed row of `rank` (-1 = padding).  Host-only; needs no GPU."""
+    L = load_library()
+    n = C.c_uint32()
+    _check(L.rt_b200_strip_layout(height, strip_rows, rank, world_size, None, 0, C.byref(n)))
+    rows = np.empty(n.value, dtype=np.int32)
+    _check(L.rt_b200_strip_layout(height, strip_rows, rank, world_size, _dp(rows), rows.size, C.byref(n)))
+    return rows
 
 
 def comm_unique_id() -> bytes:

@@ -130,6 +130,14 @@ struct rt_b200_ctx {
 
 namespace {
 
+// rows of one rank's packed buffer
+int packed_rows(int height, int strip_rows, int world)
+{
+    if (world == 1) return height;
+    const int n_strips = (height + strip_rows - 1) / strip_rows;
+    return ((n_strips + world - 1) / world) * strip_rows;
+}
+
 int free_buffers(rt_b200_ctx *c)
 {
     if (c->d_local) cudaFree(c->d_local);
@@ -143,9 +151,7 @@ int ensure_buffers(rt_b200_ctx *c)
 {
     if (!c->buffers_dirty) return RT_B200_OK;
     free_buffers(c);
-    const int n_strips = (c->height + c->strip_rows - 1) / c->strip_rows;
-    const int strips_per_rank = (n_strips + c->world - 1) / c->world;
-    c->local_rows = (c->world == 1) ? c->height : strips_per_rank * c->strip_rows;
+    c->local_rows = packed_rows(c->height, c->strip_rows, c->world);
     const size_t row_bytes = sizeof(uchar4) * (size_t) c->width;
     CUDA_TRY(cudaMalloc((void **) &c->d_local, row_bytes * c->local_rows));
     if (c->world > 1) {
@@ -468,6 +474,24 @@ int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
     }
     else {
         return fail(RT_B200_ERR_ARG, "unknown option '%s'", name);
+    }
+    return RT_B200_OK;
+}
+
+int rt_b200_strip_layout(uint32_t px_height, uint32_t strip_rows, int rank, int world_size, int32_t *image_rows,
+                         size_t capacity, uint32_t *local_rows)
+{
+    if (px_height == 0 || strip_rows == 0 || world_size < 1 || rank < 0 || rank >= world_size || !local_rows)
+        return fail(RT_B200_ERR_ARG, "bad strip layout query");
+    const int eff_strip = (world_size == 1) ? (int) px_height : (int) strip_rows;
+    const int rows = packed_rows((int) px_height, (int) strip_rows, world_size);
+    *local_rows = (uint32_t) rows;
+    if (image_rows) {
+        if (capacity < (size_t) rows) return fail(RT_B200_ERR_ARG, "image_rows holds %zu entries, need %d", capacity, rows);
+        for (int i = 0; i < rows; i++) {
+            int y = rt::local_to_image_row(i, eff_strip, rank, world_size);
+            image_rows[i] = y < (int) px_height ? y : -1;
+        }
     }
     return RT_B200_OK;
 }

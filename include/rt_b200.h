@@ -110,6 +110,14 @@ int rt_b200_get_timing(rt_b200_ctx *ctx, float out_ms[2]);
 /* Structural class counts of the uploaded scene: planes, spheres, quadrics, cubics. */
 int rt_b200_get_class_counts(rt_b200_ctx *ctx, uint32_t out[4]);
 
+/* Host-only helper (needs no GPU): the strip interleave of the multi-GPU split.  Rank r of world_size owns
+ * the strips s (of strip_rows image rows each) with s % world_size == r and stores them packed, padded to
+ * ceil(n_strips / world_size) strips so that every rank contributes the same byte count to the all-gather.
+ * *local_rows receives the packed row count; image_rows (may be NULL; capacity entries) receives, for each
+ * packed row, the image row it holds or -1 for a padding row.  world_size == 1: the identity. */
+int rt_b200_strip_layout(uint32_t px_height, uint32_t strip_rows, int rank, int world_size, int32_t *image_rows,
+                         size_t capacity, uint32_t *local_rows);
+
 /* Library build tag, e.g. "rt_b200 0.1 sm_100a". */
 const char *rt_b200_version(void);
 

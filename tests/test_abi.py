@@ -1,0 +1,80 @@
+"""CPU: the C-ABI shared library loads and exports every symbol include/rt_b200.h declares; without a GPU the
+compute entry points fail loudly (no CPU fallback)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib(pkg):
+    from cuda_ray_tracer_b200 import binding, build
+    build.build()
+    return binding.load_library()
+
+
+def test_header_symbols_exported(pkg, lib):
+    from cuda_ray_tracer_b200 import binding
+    header = open(os.path.join(ROOT, "include", "rt_b200.h")).read()
+    declared = sorted(set(re.findall(r"^(?:int|const char \*)\s*(rt_b200_[a-z_0-9]+)\s*\(", header, re.M)))
+    assert declared == sorted(binding.EXPORTS)
+    for name in declared:
+        assert hasattr(lib, name), name
+
+
+def test_no_oracle_in_product(pkg):
+    """The product must never route through the CPU checkers."""
+    pkg_dir = os.path.join(ROOT, "cuda-ray-tracer_b200")
+    for dirpath, _, files in os.walk(pkg_dir):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "oracle_py" not in text and "librt_oracle" not in text and "libref_cpu" not in text, f
+    import subprocess
+    from cuda_ray_tracer_b200 import binding
+    needed = subprocess.run(["ldd", binding.LIB_PATH], capture_output=True, text=True).stdout
+    assert "oracle" not in needed and "ref_cpu" not in needed
+
+
+def test_version_and_strip_layout(pkg, lib):
+    from cuda_ray_tracer_b200 import binding
+    assert b"sm_100a" in lib.rt_b200_version()
+    assert binding.strip_layout(10, 4, 0, 1).tolist() == list(range(10))
+    for h, s, w in [(20, 4, 2), (2160, 8, 8), (450, 8, 4), (7, 3, 2), (5, 8, 4)]:
+        seen = []
+        sizes = set()
+        for r in range(w):
+            rows = binding.strip_layout(h, s, r, w)
+            sizes.add(len(rows))
+            seen.extend(int(y) for y in rows if y >= 0)
+        assert len(sizes) == 1                      # equal contribution per rank (all-gather requirement)
+        assert sorted(seen) == list(range(h))       # every image row owned exactly once
+
+
+def test_argument_errors_and_no_gpu(pkg, lib):
+    from cuda_ray_tracer_b200 import binding
+    from cuda_ray_tracer_b200 import scene as S
+    h = C.c_void_p()
+    bg = np.zeros(3, dtype=np.float32)
+    rc = lib.rt_b200_upload_scene(C.byref(h), 0, 10, 1.0, bg.ctypes.data_as(C.c_void_p), 5, None, 0, None, 0, 0, 0, 1)
+    assert rc == 1 and b"empty frame" in lib.rt_b200_last_error()
+    rc = lib.rt_b200_upload_scene(C.byref(h), 8, 8, 1.0, bg.ctypes.data_as(C.c_void_p), 5, None, 0, None, 0, 0, 2, 2)
+    assert rc == 1 and b"bad rank" in lib.rt_b200_last_error()
+    assert lib.rt_b200_update(None, None, None) == 1
+    assert lib.rt_b200_gather(None, None, 0, None) == 1
+    assert lib.rt_b200_destroy(None) == 0
+    try:
+        import torch
+        has_gpu = torch.cuda.is_available()
+    except Exception:
+        has_gpu = False
+    if not has_gpu:
+        sc = S.Scene(8, 8, 1.0, bg, 5)
+        with pytest.raises(binding.RtError, match="rt_b200 error 2"):   # RT_B200_ERR_CUDA: fails loudly, no fallback
+            binding.Renderer(sc)
+        with pytest.raises(binding.RtError, match="before init_update"):
+            binding.update(np.eye(4).reshape(16))

@@ -1,0 +1,198 @@
+"""GPU (-m gpu): the CUDA path, called through the C ABI, against the CPU oracle.
+
+Tolerance (north_star / SURVEY.md §8c): every 8-bit channel within +-1 LSB; at most 0.1 % of pixels may differ
+more.  The exact FP64 kernel (option kernel=0) is additionally expected to be almost byte-identical."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from parity import assert_parity, compare_frames
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SCENES = ["20spheres", "quadratic", "cubic", "cayley", "clebsch", "dingdong", "monkey_saddle", "reflection_test"]
+KERNELS = [0, 1]
+
+
+@pytest.fixture(scope="module")
+def rt(pkg):
+    from cuda_ray_tracer_b200 import binding
+    binding.load_library()          # raises if the CUDA library is missing: no fallback
+    return binding
+
+
+def _load(pkg, scenes_dir, name, **over):
+    sc = pkg.load_from_file(os.path.join(scenes_dir, name + ".yml"))
+    return sc.with_overrides(**over) if over else sc
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("name", SCENES)
+def test_bundled_scenes_native_resolution(pkg, rt, oracle, scenes_dir, name, kernel):
+    from cuda_ray_tracer_b200 import camera
+    sc = _load(pkg, scenes_dir, name)
+    port = oracle.PortOracle(sc)
+    with rt.Renderer(sc) as r:
+        r.set_option("kernel", kernel)
+        for pose in ("identity", "pose_a", "pose_b"):
+            m = camera.TEST_POSES[pose]
+            ref_rgb, _, cnt = port.render_rows(m, threads=os.cpu_count(), count=True)
+            r.update(m)
+            res = assert_parity(r.gather(), oracle.quantize_rgba8(ref_rgb), "{}/{}".format(name, pose))
+            assert res["exact_frac"] > 0.999, res
+            c = r.counters()
+            if res["outliers"] == 0 and res["exact_frac"] == 1.0:
+                # same decisions everywhere -> same ray census as the reference would have executed
+                for k_gpu, k_cpu in (("primary_rays", "primary_rays"), ("reflection_rays", "reflection_rays"),
+                                     ("shadow_rays", "shadow_rays"), ("hits", "hits"), ("lit", "lit")):
+                    assert c[k_gpu] == cnt[k_cpu], (k_gpu, c, cnt)
+            assert c["primary_rays"] == sc.px_width * sc.px_height
+            assert c["shadow_rays"] == c["hits"] * len(sc.lights)
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_golden_small_frames(pkg, rt, scenes_dir, kernel):
+    """Against fixtures minted from the unmodified reference CPU back-end (tests/golden/make_golden.py)."""
+    from cuda_ray_tracer_b200 import camera
+    meta = json.load(open(os.path.join(HERE, "golden", "golden.json")))["small"]
+    frames = np.load(os.path.join(HERE, "golden", "frames_160x120.npz"))
+    for name in SCENES:
+        sc = _load(pkg, scenes_dir, name, width=meta["width"], height=meta["height"],
+                   max_reflections=meta["max_reflections"])
+        with rt.Renderer(sc) as r:
+            r.set_option("kernel", kernel)
+            for pose in meta["poses"]:
+                r.update(camera.TEST_POSES[pose])
+                assert_parity(r.gather(), frames["{}/{}".format(name, pose)], "{}/{}".format(name, pose))
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("name", ["reflection_test", "dingdong", "cayley"])
+def test_full_size_properties_4k(pkg, rt, oracle, scenes_dir, name, kernel):
+    """BASELINE.json sizes (3840x2160, 4 bounces): the full CPU frame takes too long for a test, so check a
+    sparse oracle (random pixels + whole rows) and size-independent properties."""
+    from cuda_ray_tracer_b200 import camera
+    sc = _load(pkg, scenes_dir, name, width=3840, height=2160, max_reflections=4)
+    m = camera.TEST_POSES["pose_a"]
+    port = oracle.PortOracle(sc)
+    with rt.Renderer(sc) as r:
+        r.set_option("kernel", kernel)
+        r.update(m)
+        a = r.gather()
+        r.update(m)
+        assert np.array_equal(a, r.gather())                              # deterministic / idempotent
+        c = r.counters()
+        assert c["primary_rays"] == 3840 * 2160 and c["shadow_rays"] == c["hits"] * len(sc.lights)
+        rng = np.random.default_rng(1)
+        xy = np.stack([rng.integers(0, 3840, 20000), rng.integers(0, 2160, 20000)], axis=1).astype(np.int32)
+        ref = oracle.quantize_rgba8(port.render_pixels(m, xy))
+        assert_parity(a[xy[:, 1], xy[:, 0]][None], ref[None], name + " sparse pixels")
+        rows = [0, 1079, 1080, 2159]
+        for y in rows:
+            rgb, _ = port.render_rows(m, y, y + 1, threads=1)
+            assert_parity(a[y:y + 1], oracle.quantize_rgba8(rgb), "{} row {}".format(name, y))
+    # strip split: two ranks' rows merged == the single-GPU frame, byte for byte
+    merged = np.zeros_like(a)
+    for rank in range(2):
+        with rt.Renderer(sc, rank=rank, world_size=2) as r:
+            r.set_option("kernel", kernel)
+            r.set_option("strip_rows", 8)
+            r.update(m)
+            part = r.gather()
+            own = rt.strip_layout(2160, 8, rank, 2)
+            own = own[own >= 0]
+            merged[own] = part[own]
+            other = np.setdiff1d(np.arange(2160), own)
+            assert not part[other].any()
+    assert np.array_equal(merged, a)
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_edge_cases(pkg, rt, oracle, kernel):
+    from cuda_ray_tracer_b200 import camera
+    from cuda_ray_tracer_b200 import scene as S
+    bg = np.array([0.25, 0.5, 0.75], dtype=np.float32)
+
+    def check(sc, poses=("identity", "pose_b")):
+        port = oracle.PortOracle(sc)
+        with rt.Renderer(sc) as r:
+            r.set_option("kernel", kernel)
+            for pose in poses:
+                m = camera.TEST_POSES[pose]
+                r.update(m)
+                img = r.gather()
+                res = compare_frames(img, oracle.quantize_rgba8(port.render(m)))
+                assert res["outliers"] <= max(1, int(1e-3 * res["pixels"])) and res["max_diff"] <= 255, res
+                if res["pixels"] >= 1000:
+                    assert res["outlier_frac"] <= 1e-3, res
+        return img
+
+    # empty scene: every pixel is the background
+    img = check(S.Scene(33, 17, np.radians(60.0), bg, 5))
+    assert (img == oracle.quantize_rgba8(bg.reshape(1, 3))[0]).all()
+    # 1x1 frame, and sizes that are not multiples of the tile
+    obj = lambda k, refl=0.0, col=(0.8, 0.6, 0.2): S.make_object(k, refl, col)
+    lights = np.array([S.light_directional(2.0, [0.3, -1, 0.5], [1, 1, 1]),
+                       S.light_spherical(300.0, [2, 5, 3], [1, 0.5, 0.25])], dtype=S.LIGHT_DTYPE)
+    for w, h in [(1, 1), (37, 19), (130, 9), (8, 64)]:
+        sc = S.Scene(w, h, np.radians(50.0), bg, 3)
+        sc.objects = np.array([obj(S.surface_sphere([0, 0, 8], 2.0)), obj(S.surface_plane([0, -2, 0], [0, 1, 0]), 0.4)],
+                              dtype=S.OBJECT_DTYPE)
+        sc.lights = lights
+        check(sc)
+    # objects but no lights: hits are black; reflective with max_reflections 0
+    sc = S.Scene(64, 48, np.radians(50.0), bg, 0)
+    sc.objects = np.array([obj(S.surface_sphere([0, 0, 8], 2.0), 0.5)], dtype=S.OBJECT_DTYPE)
+    check(sc)
+    # two facing mirrors + a sphere: deep reflection chains, up to max_reflections = 7
+    sc = S.Scene(96, 64, np.radians(70.0), bg, 7)
+    sc.objects = np.array([obj(S.surface_plane([0, -2, 0], [0, 1, 0]), 0.8), obj(S.surface_plane([0, 3, 0], [0, -1, 0]), 0.7),
+                           obj(S.surface_sphere([0.5, 0, 7], 1.0), 0.5, (0.9, 0.1, 0.1))], dtype=S.OBJECT_DTYPE)
+    sc.lights = lights
+    check(sc)
+    # every structural class at once, shuffled order (class sort must keep the lowest-index tie rule),
+    # including a duplicated object (exact tie in t) with different colours
+    k_quad = np.zeros(20); k_quad[10] = 0.1; k_quad[12] = 0.1; k_quad[17] = 1.0; k_quad[19] = 20.0
+    k_cub = S.surface_ding_dong([0, 0, 10])
+    sc = S.Scene(120, 90, np.radians(60.0), bg, 4)
+    sc.objects = np.array([obj(k_cub), obj(S.surface_sphere([3, 1, 9], 1.0), 0.3), obj(k_quad),
+                           obj(S.surface_plane([0, -30, 0], [0, 1, 0]), 0.0, (0.1, 0.5, 0.1)),
+                           obj(S.surface_sphere([3, 1, 9], 1.0), 0.0, (0.1, 0.1, 0.9)),
+                           obj(S.surface_sphere([-3, 1, 9], 1.5), 0.2)], dtype=S.OBJECT_DTYPE)
+    sc.lights = lights
+    check(sc, poses=("identity", "pose_a", "pose_b"))
+
+
+def test_update_h_call_surface(pkg, rt, oracle, scenes_dir):
+    """init_update / update / cleanup_update with one global context, as the reference's update.h:6-8."""
+    from cuda_ray_tracer_b200 import camera
+    sc = _load(pkg, scenes_dir, "monkey_saddle", width=200, height=150)
+    with pytest.raises(rt.RtError):
+        rt.update(camera.IDENTITY)
+    rt.init_update(0, sc)
+    with pytest.raises(rt.RtError, match="before the first"):
+        rt.gather()
+    ms = rt.update(camera.TEST_POSES["initial"])
+    assert ms > 0.0
+    assert_parity(rt.gather(), oracle.quantize_rgba8(oracle.PortOracle(sc).render(camera.TEST_POSES["initial"])))
+    rt.cleanup_update()
+    rt.cleanup_update()
+    with pytest.raises(rt.RtError):
+        rt.update(camera.IDENTITY)
+
+
+def test_reference_build_agrees_on_gpu_box(pkg, rt, oracle, scenes_dir):
+    """The prebuilt reference CPU library travels to the GPU box: GPU vs the reference itself (not the port)."""
+    if not oracle.have_ref():
+        pytest.skip("oracle/_ref/libref_cpu.so not present")
+    from cuda_ray_tracer_b200 import camera
+    for name in ("cayley", "dingdong", "20spheres"):
+        sc = _load(pkg, scenes_dir, name, width=400, height=300, max_reflections=4)
+        ref = oracle.RefCpu(sc)
+        rgb, _ = ref.update(camera.TEST_POSES["pose_a"])
+        with rt.Renderer(sc) as r:
+            r.update(camera.TEST_POSES["pose_a"])
+            assert_parity(r.gather(), oracle.quantize_rgba8(rgb), name)
