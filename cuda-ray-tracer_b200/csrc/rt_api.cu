@@ -115,9 +115,13 @@ struct rt_b200_ctx {
     uchar4 *d_gathered = nullptr;   // [world][local_rows][width] (world > 1)
     uchar4 *d_frame = nullptr;      // [height][width] (world > 1)
     unsigned long long *d_counters = nullptr;
+    unsigned long long *d_tile_counter = nullptr;
+    unsigned *d_cubic_mask = nullptr;
+    float sphere_r2_max = 0.0f;
+    int shadow_cache = -1;
     bool buffers_dirty = true;
 
-    int kernel_kind = 0;
+    int kernel_kind = 1;
     bool count = true;
     bool rendered = false;
 
@@ -220,7 +224,8 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     std::vector<float4> sphere_f, material(n_objects);
     std::vector<double> quadric, cubic, coef_full(20 * n_objects);
     std::vector<int> orig[4];
-    float center_max = 0.0f;
+    std::vector<unsigned> cubic_mask;
+    float center_max = 0.0f, r2_max = 0.0f;
     const char *obj_bytes = static_cast<const char *>(objects);
     for (size_t i = 0; i < n_objects; i++) {
         double k[20];
@@ -242,15 +247,22 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
                 double cx = -0.5 * k[rt::LX], cy = -0.5 * k[rt::LY], cz = -0.5 * k[rt::LZ];
                 double r2 = cx * cx + cy * cy + cz * cz - k[rt::CC];
                 sphere_f.push_back(make_float4((float) cx, (float) cy, (float) cz, (float) r2));
+                r2_max = fmaxf(r2_max, nextafterf((float) fabs(r2), INFINITY));
                 center_max = fmaxf(center_max, fmaxf(fabsf((float) cx), fmaxf(fabsf((float) cy), fabsf((float) cz))));
                 break;
             }
             case rt::CLS_QUADRIC:
                 for (int j = rt::X2; j <= rt::CC; j++) quadric.push_back(k[j]);
                 break;
-            case rt::CLS_CUBIC:
-                for (int j = 0; j < 20; j++) cubic.push_back(k[j]);
+            case rt::CLS_CUBIC: {
+                unsigned mask = 0;
+                for (int j = 0; j < 20; j++) {
+                    cubic.push_back(k[j]);
+                    if (k[j] != 0.0) mask |= 1u << j;
+                }
+                cubic_mask.push_back(mask);
                 break;
+            }
         }
     }
     std::vector<int> orig_index;
@@ -282,6 +294,9 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     up(upload(material, &c->d_material), "materials");
     up(upload(orig_index, &c->d_orig), "index map");
     up(upload(ldev, &c->d_lights), "lights");
+    up(upload(cubic_mask, &c->d_cubic_mask), "cubic masks");
+    up(cudaMalloc((void **) &c->d_tile_counter, sizeof(unsigned long long)), "tile counter");
+    c->sphere_r2_max = r2_max;
     up(cudaMalloc((void **) &c->d_counters, sizeof(unsigned long long) * rt::CNT_COUNT), "counters");
     up(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "stream");
     up(cudaEventCreate(&c->ev_start), "event");
@@ -347,7 +362,13 @@ int rt_b200_update(rt_b200_ctx *c, const double camera_matrix[16], float *elapse
 
     if (c->count) CUDA_TRY(cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long) * rt::CNT_COUNT, c->stream));
     CUDA_TRY(cudaEventRecord(c->ev_start, c->stream));
-    CUDA_TRY(rt::launch_render_exact(c->view, f, c->stream));
+    if (c->kernel_kind == 0) {
+        CUDA_TRY(rt::launch_render_exact(c->view, f, c->stream));
+    }
+    else {
+        rt::WaveLaunch wl{c->d_tile_counter, c->d_cubic_mask, c->sphere_r2_max, c->shadow_cache};
+        CUDA_TRY(rt::launch_render_wave(c->view, f, wl, c->stream));
+    }
     CUDA_TRY(cudaEventRecord(c->ev_render, c->stream));
     if (c->world > 1 && c->comm) {
         const size_t bytes = sizeof(uchar4) * (size_t) c->width * c->local_rows;
@@ -413,6 +434,8 @@ int rt_b200_destroy(rt_b200_ctx *c)
     cudaFree(c->d_orig);
     cudaFree(c->d_lights);
     cudaFree(c->d_counters);
+    cudaFree(c->d_tile_counter);
+    cudaFree(c->d_cubic_mask);
     if (c->ev_start) cudaEventDestroy(c->ev_start);
     if (c->ev_render) cudaEventDestroy(c->ev_render);
     if (c->ev_end) cudaEventDestroy(c->ev_end);
@@ -468,6 +491,10 @@ int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
             c->strip_rows = (int) value;
             c->buffers_dirty = true;
         }
+    }
+    else if (!std::strcmp(name, "shadow_cache")) {
+        if (value < -1 || value > 1) return fail(RT_B200_ERR_ARG, "shadow_cache must be -1, 0 or 1");
+        c->shadow_cache = (int) value;
     }
     else if (!std::strcmp(name, "count")) {
         c->count = value != 0;

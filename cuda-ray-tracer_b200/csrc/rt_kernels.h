@@ -9,6 +9,15 @@ namespace rt {
 // Exact FP64 kernel, one thread per pixel (the known-good device path every faster kernel is diffed against).
 cudaError_t launch_render_exact(const SceneView &scene, const FrameParams &frame, cudaStream_t stream);
 
+// Block-local wavefront kernel (rt_wave.cu).
+struct WaveLaunch {
+    unsigned long long *tile_counter;   // device, one 64-bit slot
+    const unsigned *cubic_mask;         // device, [n_cubic] non-zero coefficient masks
+    float sphere_r2_max;                // max r^2 over sphere-class objects (filter error bound)
+    int shadow_cache;                   // 1 / 0 / -1 = automatic (on when the scene has >= 8 objects)
+};
+cudaError_t launch_render_wave(const SceneView &scene, const FrameParams &frame, const WaveLaunch &wl, cudaStream_t stream);
+
 // Undo the strip interleave after the all-gather: gathered = [world][local_rows][width] -> frame[height][width].
 cudaError_t launch_unpack_strips(const uchar4 *gathered, uchar4 *frame, int width, int height, int strip_rows,
                                  int world, int local_rows, cudaStream_t stream);

@@ -55,7 +55,7 @@ __device__ __forceinline__ double solve_quadratic_or_linear(double t2, double t1
     return -1.0;
 }
 
-__device__ __noinline__ double solve_cubic(double t3, double t2, double t1, double t0)
+static __device__ __noinline__ double solve_cubic(double t3, double t2, double t1, double t0)
 {
     t2 /= t3;
     t1 /= t3;

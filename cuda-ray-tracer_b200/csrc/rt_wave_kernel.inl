@@ -1,0 +1,330 @@
+// rt_wave_kernel.inl — body of the wavefront kernel (included by rt_wave.cu).
+namespace rt {
+
+namespace {
+
+// Write finished pixels of a PRIMARY wave.  Lanes 4i..4i+3 of a warp hold four horizontally adjacent pixels
+// (8x4 sub-tile per warp); when all four are final the group leader stores them as one 128-bit uchar4x4.
+__device__ __forceinline__ void store_primary(uchar4 *out, size_t index, bool final_px, uchar4 px, bool vec_ok)
+{
+    const unsigned lane = threadIdx.x & 31;
+    const unsigned done = __ballot_sync(0xffffffffu, final_px);
+    const unsigned group = (done >> (lane & ~3u)) & 0xfu;
+    unsigned v = *reinterpret_cast<unsigned *>(&px);
+    const unsigned v1 = __shfl_down_sync(0xffffffffu, v, 1);
+    const unsigned v2 = __shfl_down_sync(0xffffffffu, v, 2);
+    const unsigned v3 = __shfl_down_sync(0xffffffffu, v, 3);
+    if (vec_ok && group == 0xfu) {
+        if ((lane & 3u) == 0) *reinterpret_cast<uint4 *>(out + index) = make_uint4(v, v1, v2, v3);
+    }
+    else if (final_px) {
+        out[index] = px;
+    }
+}
+
+__device__ __forceinline__ float blend(float out, float ratio, float c) { return (1.0f - ratio) * out + ratio * c; }
+
+} // namespace
+
+template <bool COUNT>
+__global__ void __launch_bounds__(WAVE, 2)
+render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ FrameParams f,
+                   const __grid_constant__ WaveConfig cfg)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Pool &pool = *reinterpret_cast<Pool *>(smem_raw);
+    WaveHits &wh = *reinterpret_cast<WaveHits *>(smem_raw + align16(sizeof(Pool)));
+    WaveCtl &ctl = *reinterpret_cast<WaveCtl *>(smem_raw + align16(sizeof(Pool)) + align16(sizeof(WaveHits)));
+    unsigned char *sp = smem_raw + wave_fixed_smem();
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    // ---- stage the scene once per CTA ----------------------------------------------------------------
+    SceneSmem s;
+    {
+        double4 *pl = reinterpret_cast<double4 *>(sp);
+        sp += align16(sizeof(double4) * g.n_plane);
+        for (int i = tid; i < g.n_plane; i += WAVE) pl[i] = g.plane[i];
+        s.plane = pl;
+        if (cfg.spheres_in_smem) {
+            float4 *sf = reinterpret_cast<float4 *>(sp);
+            sp += align16(sizeof(float4) * g.n_sphere);
+            for (int i = tid; i < g.n_sphere; i += WAVE) sf[i] = g.sphere_f[i];
+            s.sphere_f = sf;
+        }
+        else {
+            s.sphere_f = g.sphere_f;
+        }
+        double *qd = reinterpret_cast<double *>(sp);
+        sp += align16(sizeof(double) * 10 * g.n_quadric);
+        for (int i = tid; i < 10 * g.n_quadric; i += WAVE) qd[i] = g.quadric[i];
+        s.quadric = qd;
+        double *cb = reinterpret_cast<double *>(sp);
+        sp += align16(sizeof(double) * 20 * g.n_cubic);
+        for (int i = tid; i < 20 * g.n_cubic; i += WAVE) cb[i] = g.cubic[i];
+        s.cubic = cb;
+        unsigned *cm = reinterpret_cast<unsigned *>(sp);
+        sp += align16(sizeof(unsigned) * g.n_cubic);
+        for (int i = tid; i < g.n_cubic; i += WAVE) cm[i] = cfg.cubic_mask[i];
+        s.cubic_mask = cm;
+        LightDev *lt = reinterpret_cast<LightDev *>(sp);
+        for (int i = tid; i < g.n_lights; i += WAVE) lt[i] = g.lights[i];
+        s.lights = lt;
+        if (tid == 0) ctl.pool_count = 0;
+        if (tid < LIGHT_CHUNK) ctl.shadow_cache[tid] = -1;
+    }
+    __syncthreads();
+
+    Tally tl;
+    tl.clear();
+    const d3 cam_origin = d3{f.origin[0], f.origin[1], f.origin[2]};
+    const int n_tiles = cfg.tiles_x * cfg.tiles_y;
+    const bool vec_ok = (f.width & 3) == 0;
+    bool tiles_left = true;
+    unsigned waves = 0;
+
+    for (;;) {
+        if (COUNT && (++waves & 63u) == 0) {   // keep the 32-bit per-thread tallies far from overflow
+            flush_tally(tl, f.counters);
+            tl.clear();
+        }
+        // ---- choose the next wave: pooled bounce rays when a full wave is waiting (or nothing else is left) ----
+        if (tid == 0) {
+            ctl.tile = -1;
+            if (ctl.pool_count < WAVE && tiles_left) ctl.tile = (int) atomicAdd(cfg.tile_counter, 1ULL);
+            ctl.n_hits = 0;
+        }
+        __syncthreads();
+        int tile = ctl.tile;
+        if (tile >= n_tiles) {
+            tiles_left = false;
+            tile = -1;
+        }
+        const int pooled = ctl.pool_count;
+        if (tile < 0 && pooled == 0) {
+            if (!tiles_left) break;
+            continue;   // unreachable in practice: tile < 0 with tiles_left means pool >= WAVE
+        }
+        __syncthreads();   // everyone has read ctl.tile / pool_count before they change
+
+        // ---- ray of this thread -----------------------------------------------------------------------
+        bool active;
+        d3 o, d;
+        float out_r = 0.f, out_g = 0.f, out_b = 0.f, ratio = 1.0f;
+        int bounces = 0, pixel = 0;
+        const bool primary = tile >= 0;
+        if (primary) {
+            const int tx = tile % cfg.tiles_x, ty = tile / cfg.tiles_x;
+            const int x = tx * 32 + (warp & 3) * 8 + (lane & 7);
+            const int lrow = ty * 8 + (warp >> 2) * 4 + (lane >> 3);
+            const int y = local_to_image_row(lrow, f.strip_rows, f.rank, f.world);
+            const bool in_buf = x < f.width && lrow < f.local_rows;
+            active = in_buf && y < f.height;
+            pixel = lrow * f.width + x;
+            if (in_buf && !active) f.out[pixel] = make_uchar4(0, 0, 0, 0);   // padding row past the image
+            if (active) {
+                o = cam_origin;
+                d = primary_dir(f, cam_origin, x, y);
+                if (COUNT) tl.n[CNT_PRIMARY]++;
+            }
+        }
+        else {
+            const int take = pooled < WAVE ? pooled : WAVE;
+            const int base = pooled - take;
+            active = tid < take;
+            if (active) {
+                const int r = base + tid;
+                o = d3{pool.ox[r], pool.oy[r], pool.oz[r]};
+                d = d3{pool.dx[r], pool.dy[r], pool.dz[r]};
+                out_r = pool.out_r[r]; out_g = pool.out_g[r]; out_b = pool.out_b[r];
+                ratio = pool.ratio[r];
+                pixel = pool.pixel[r];
+                bounces = pool.bounces[r];
+            }
+            __syncthreads();
+            if (tid == 0) ctl.pool_count = base;
+        }
+
+        // ---- phase A + B: nearest hit, hit record, compact hit list ---------------------------------------
+        int obj = -1;
+        if (active) {
+            Hit h = nearest_hit_wave(g, s, cfg, o, d, tl);
+            if (h.slot >= 0) {
+                obj = h.orig;
+                const d3 p = d3{o.x + h.t * d.x, o.y + h.t * d.y, o.z + h.t * d.z};
+                const d3 n = surface_normal(g.coef_full + 20 * obj, p);
+                wh.px[tid] = p.x; wh.py[tid] = p.y; wh.pz[tid] = p.z;
+                wh.nx[tid] = n.x; wh.ny[tid] = n.y; wh.nz[tid] = n.z;
+                if (COUNT) tl.n[CNT_HITS]++;
+            }
+        }
+        const bool hit = obj >= 0;
+        bool final_px = false;
+        if (active && !hit) {
+            // miss: background (primary) or blend towards it (update-cpu.cpp:94-96,112-115)
+            if (primary) { out_r = f.bg[0]; out_g = f.bg[1]; out_b = f.bg[2]; }
+            else { out_r = blend(out_r, ratio, f.bg[0]); out_g = blend(out_g, ratio, f.bg[1]); out_b = blend(out_b, ratio, f.bg[2]); }
+            final_px = true;
+        }
+        {
+            const unsigned m = __ballot_sync(0xffffffffu, hit);
+            if (lane == 0) ctl.warp_base[warp] = __popc(m);
+            __syncthreads();
+            int base = 0;
+            for (int w = 0; w < warp; w++) base += ctl.warp_base[w];
+            if (hit) wh.hitlist[base + __popc(m & ((1u << lane) - 1u))] = (unsigned short) tid;
+            if (tid == WAVE - 1) ctl.n_hits = base + __popc(m);
+        }
+        __syncthreads();
+        const int n_hits = ctl.n_hits;
+
+        // ---- phases C + D per chunk of 32 lights ---------------------------------------------------------------
+        float acc_r = 0.f, acc_g = 0.f, acc_b = 0.f;
+        float4 mat = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (hit) mat = __ldg(&g.material[obj]);
+        for (int l0 = 0; l0 < g.n_lights; l0 += LIGHT_CHUNK) {
+            const int lc = min(LIGHT_CHUNK, g.n_lights - l0);
+            if (hit) wh.occluded[tid] = 0u;
+            __syncthreads();
+            // C: task = (light j, hit i), light-major
+            for (int task = tid; task < n_hits * lc; task += WAVE) {
+                const int j = task / n_hits;
+                const int k = wh.hitlist[task - j * n_hits];
+                const LightDev l = s.lights[l0 + j];
+                const d3 p = d3{wh.px[k], wh.py[k], wh.pz[k]};
+                const d3 n = d3{wh.nx[k], wh.ny[k], wh.nz[k]};
+                const d3 so = d3{p.x + RT_SHADOW_BIAS * n.x, p.y + RT_SHADOW_BIAS * n.y, p.z + RT_SHADOW_BIAS * n.z};
+                double max_t;
+                const d3 sd = shadow_dir(l, p, max_t);
+                if (COUNT) tl.n[CNT_SHADOW]++;
+                bool occ = false;
+                if (cfg.use_shadow_cache) {
+                    const int cs = ctl.shadow_cache[j];
+                    if (cs >= 0) occ = blocks(intersect_slot(g, s, cs, so, sd, tl), max_t);
+                }
+                if (!occ) {
+                    const int by = l.is_spherical ? occluder_wave<true>(g, s, cfg, so, sd, max_t, tl)
+                                                  : occluder_wave<false>(g, s, cfg, so, sd, max_t, tl);
+                    occ = by >= 0;
+                    if (occ && cfg.use_shadow_cache) ctl.shadow_cache[j] = by;   // benign race: any occluder will do
+                }
+                if (occ) atomicOr(&wh.occluded[k], 1u << j);
+            }
+            __syncthreads();
+            // D (part 1): sum the unshadowed lights of this chunk in index order
+            if (hit) {
+                const unsigned occ = wh.occluded[tid];
+                const d3 p = d3{wh.px[tid], wh.py[tid], wh.pz[tid]};
+                const d3 n = d3{wh.nx[tid], wh.ny[tid], wh.nz[tid]};
+                float3 acc = make_float3(acc_r, acc_g, acc_b);
+                const float3 oc = make_float3(mat.y, mat.z, mat.w);
+                for (int j = 0; j < lc; j++) {
+                    if (!((occ >> j) & 1u)) {
+                        shade_light(s.lights[l0 + j], p, n, oc, acc);
+                        if (COUNT) tl.n[CNT_LIT]++;
+                    }
+                }
+                acc_r = acc.x; acc_g = acc.y; acc_b = acc.z;
+            }
+            __syncthreads();
+        }
+
+        // ---- phase D (part 2): clamp, blend, bounce ---------------------------------------------------------------
+        bool spawn = false;
+        d3 no, nd;
+        if (hit) {
+            const float cr = (acc_r < 1.0f) ? acc_r : 1.0f;   // glm::min(vec3(1), c), update-cpu.cpp:77
+            const float cg = (acc_g < 1.0f) ? acc_g : 1.0f;
+            const float cb = (acc_b < 1.0f) ? acc_b : 1.0f;
+            if (primary) { out_r = cr; out_g = cg; out_b = cb; }
+            else { out_r = blend(out_r, ratio, cr); out_g = blend(out_g, ratio, cg); out_b = blend(out_b, ratio, cb); }
+            final_px = true;
+            if (mat.x > RT_EPS) {   // update-cpu.cpp:100-111
+                ratio *= mat.x;
+                if (bounces == f.max_reflections) {
+                    out_r = blend(out_r, ratio, f.bg[0]); out_g = blend(out_g, ratio, f.bg[1]); out_b = blend(out_b, ratio, f.bg[2]);
+                }
+                else {
+                    bounces++;
+                    const d3 p = d3{wh.px[tid], wh.py[tid], wh.pz[tid]};
+                    const d3 n = d3{wh.nx[tid], wh.ny[tid], wh.nz[tid]};
+                    nd = reflect(d, n);
+                    no = d3{p.x + RT_SHADOW_BIAS * n.x, p.y + RT_SHADOW_BIAS * n.y, p.z + RT_SHADOW_BIAS * n.z};
+                    spawn = true;
+                    final_px = false;
+                    if (COUNT) tl.n[CNT_REFLECTION]++;
+                }
+            }
+        }
+        // append bounce rays to the pool: warp ballot + prefix popc, one shared atomic per warp
+        {
+            const unsigned m = __ballot_sync(0xffffffffu, spawn);
+            int wbase = 0;
+            if (lane == 0 && m) wbase = atomicAdd(&ctl.pool_count, __popc(m));
+            wbase = __shfl_sync(0xffffffffu, wbase, 0);
+            if (spawn) {
+                const int r = wbase + __popc(m & ((1u << lane) - 1u));
+                pool.ox[r] = no.x; pool.oy[r] = no.y; pool.oz[r] = no.z;
+                pool.dx[r] = nd.x; pool.dy[r] = nd.y; pool.dz[r] = nd.z;
+                pool.out_r[r] = out_r; pool.out_g[r] = out_g; pool.out_b[r] = out_b;
+                pool.ratio[r] = ratio;
+                pool.pixel[r] = pixel;
+                pool.bounces[r] = bounces;
+            }
+        }
+        // finished pixels leave the SM
+        const uchar4 px = pack_rgba8(out_r, out_g, out_b);
+        if (primary) store_primary(f.out, (size_t) pixel, final_px, px, vec_ok);
+        else if (final_px) f.out[pixel] = px;
+        __syncthreads();
+    }
+    if (COUNT) flush_tally(tl, f.counters);
+}
+
+static size_t g_wave_smem_limit = 0;
+
+cudaError_t launch_render_wave(const SceneView &scene, const FrameParams &frame, const WaveLaunch &wl, cudaStream_t stream)
+{
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    int n_sm = 0, max_smem = 0;
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+
+    WaveConfig cfg;
+    cfg.tiles_x = (frame.width + 31) / 32;
+    cfg.tiles_y = (frame.local_rows + 7) / 8;
+    cfg.tile_counter = wl.tile_counter;
+    cfg.cubic_mask = wl.cubic_mask;
+    cfg.sphere_r2_max = wl.sphere_r2_max;
+    cfg.use_shadow_cache = wl.shadow_cache >= 0 ? wl.shadow_cache : (scene.n_objects >= 8 ? 1 : 0);
+    size_t smem = wave_fixed_smem() + wave_scene_smem(scene, true);
+    cfg.spheres_in_smem = 1;
+    if (smem > (size_t) max_smem) {
+        cfg.spheres_in_smem = 0;
+        smem = wave_fixed_smem() + wave_scene_smem(scene, false);
+        if (smem > (size_t) max_smem) return cudaErrorInvalidConfiguration;
+    }
+    auto kern = frame.counters ? render_wave_kernel<true> : render_wave_kernel<false>;
+    if (smem > g_wave_smem_limit) {
+        e = cudaFuncSetAttribute(render_wave_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(render_wave_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e != cudaSuccess) return e;
+        g_wave_smem_limit = (size_t) max_smem;
+    }
+    int per_sm = 1;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, WAVE, smem);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) per_sm = 1;
+    const int n_tiles = cfg.tiles_x * cfg.tiles_y;
+    int grid = n_sm * per_sm;
+    if (grid > n_tiles) grid = n_tiles;
+    e = cudaMemsetAsync(wl.tile_counter, 0, sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
+    kern<<<grid, WAVE, smem, stream>>>(scene, frame, cfg);
+    return cudaGetLastError();
+}
+
+} // namespace rt
