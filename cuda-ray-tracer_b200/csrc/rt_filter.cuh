@@ -34,6 +34,7 @@ struct RayF {
     float kA1, kA0;     // margin = kA1 * q2 + kA0   (already multiplied by A, rounded up)
     float kb1, kb0;     // |b_fp32 - b_exact| <= kb1 * q2 + kb0
     float kc1, kc0;     // |c_fp32 - c_exact| <= kc1 * q2 + kc0
+    bool safe;          // false: magnitudes could overflow FP32 (inf - inf = NaN) -> skip the filter for this ray
 };
 
 __device__ __forceinline__ RayF make_rayf(const d3 &o, const d3 &d, float center_max, float r2_max)
@@ -57,7 +58,21 @@ __device__ __forceinline__ RayF make_rayf(const d3 &o, const d3 &d, float center
     // c: 4 e1 Q + 3 u Q^2 + 3 e1^2 + u r^2 + u |c|, Q <= (Q^2 / S + S) / 2
     r.kc1 = 2.0f * (2.0f * e1 / S + 5.0f * RT_U32F);
     r.kc0 = 2.0f * (2.0f * e1 * S + 3.0f * e1 * e1 + 2.0f * RT_U32F * r2_max);
+    // q2 <= 3 (omax + Cmax)^2 and A q2 must stay finite in FP32 (max 3.4e38): keep every factor below 1e9
+    r.safe = omax < 1e9f && center_max < 1e9f && r.A < 1e18f && r2_max < 1e18f;
     return r;
+}
+
+// Hot-loop half of the filter: disc + margin for one sphere (negative = the line provably misses it).
+// 14 FP32 instructions, no branch; four of these are evaluated back to back for instruction-level parallelism.
+__device__ __forceinline__ float sphere_slack(const RayF &r, const float4 s)
+{
+    const float ocx = r.ox - s.x, ocy = r.oy - s.y, ocz = r.oz - s.z;
+    const float b = fmaf(ocx, r.dx, fmaf(ocy, r.dy, ocz * r.dz));
+    const float q2 = fmaf(ocx, ocx, fmaf(ocy, ocy, ocz * ocz));
+    const float c = q2 - s.w;
+    const float disc = fmaf(b, b, -(r.A * c));
+    return disc + fmaf(q2, r.kA1, r.kA0);
 }
 
 // Outcome of the filter for one sphere {cx, cy, cz, r^2}.

@@ -35,6 +35,20 @@ __device__ __forceinline__ void consider(Hit &h, double t, int slot, int orig)
     }
 }
 
+// Same rule with the slot -> original-index lookup deferred: it is only needed on an exact tie in t.
+__device__ __forceinline__ void consider_lazy(Hit &h, double t, int slot, const int *__restrict__ orig_index)
+{
+    if (t >= RT_EPS && t < RT_MAX_T) {
+        if (t < h.t) {
+            h.t = t;
+            h.slot = slot;
+        }
+        else if (t == h.t && h.slot >= 0 && __ldg(&orig_index[slot]) < __ldg(&orig_index[h.slot])) {
+            h.slot = slot;
+        }
+    }
+}
+
 __device__ __forceinline__ Hit nearest_hit_exact(const SceneView &sc, const d3 &o, const d3 &d, Tally &tl)
 {
     Hit h;

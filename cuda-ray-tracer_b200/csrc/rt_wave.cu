@@ -33,25 +33,40 @@ __device__ __forceinline__ Hit nearest_hit_wave(const SceneView &g, const SceneS
     h.slot = -1;
     h.orig = 0x7fffffff;
     int slot = 0;
-    for (int i = 0; i < g.n_plane; i++, slot++)
-        consider(h, intersect_plane(s.plane[i], o, d), slot, __ldg(&g.orig_index[slot]));
+    for (int i = 0; i < g.n_plane; i++, slot++) consider_lazy(h, intersect_plane(s.plane[i], o, d), slot, g.orig_index);
     if (g.n_sphere > 0) {
         const RayF rf = make_rayf(o, d, g.sphere_center_max, cfg.sphere_r2_max);
         unsigned confirms = 0;
-#pragma unroll 4
-        for (int i = 0; i < g.n_sphere; i++) {
-            if (!sphere_rejected<false>(rf, s.sphere_f[i])) {
+        const int n4 = rf.safe ? (g.n_sphere & ~3) : 0;
+        int i = 0;
+        for (; i < n4; i += 4) {
+            // four independent filter evaluations, one branch: candidates are rare
+            const float s0 = sphere_slack(rf, s.sphere_f[i]), s1 = sphere_slack(rf, s.sphere_f[i + 1]);
+            const float s2 = sphere_slack(rf, s.sphere_f[i + 2]), s3 = sphere_slack(rf, s.sphere_f[i + 3]);
+            if (!(fmaxf(fmaxf(s0, s1), fmaxf(s2, s3)) < 0.0f)) {
+#pragma unroll 1
+                for (int j = i; j < i + 4; j++) {
+                    if (!sphere_rejected<false>(rf, s.sphere_f[j])) {
+                        confirms++;
+                        consider_lazy(h, intersect_sphere(g.sphere[j], o, d), slot + j, g.orig_index);
+                    }
+                }
+            }
+        }
+        for (; i < g.n_sphere; i++) {
+            if (!rf.safe || !sphere_rejected<false>(rf, s.sphere_f[i])) {
                 confirms++;
-                consider(h, intersect_sphere(g.sphere[i], o, d), slot + i, __ldg(&g.orig_index[slot + i]));
+                consider_lazy(h, intersect_sphere(g.sphere[i], o, d), slot + i, g.orig_index);
             }
         }
         slot += g.n_sphere;
         tl.n[CNT_CONFIRM] += confirms;
     }
     for (int i = 0; i < g.n_quadric; i++, slot++)
-        consider(h, intersect_quadric(s.quadric + 10 * i, o, d), slot, __ldg(&g.orig_index[slot]));
+        consider_lazy(h, intersect_quadric(s.quadric + 10 * i, o, d), slot, g.orig_index);
     for (int i = 0; i < g.n_cubic; i++, slot++)
-        consider(h, intersect_cubic_masked(s.cubic + 20 * i, s.cubic_mask[i], o, d), slot, __ldg(&g.orig_index[slot]));
+        consider_lazy(h, intersect_cubic_masked(s.cubic + 20 * i, s.cubic_mask[i], o, d), slot, g.orig_index);
+    if (h.slot >= 0) h.orig = __ldg(&g.orig_index[h.slot]);
     tl.n[CNT_T_PLANE] += g.n_plane;
     tl.n[CNT_T_SPHERE] += g.n_sphere;
     tl.n[CNT_T_QUADRIC] += g.n_quadric;
@@ -84,44 +99,81 @@ __device__ __forceinline__ double intersect_slot(const SceneView &g, const Scene
 }
 
 // ---- phase C: any occluder with EPS < t < max_t (update-cpu.cpp:66-72); returns the occluding slot or -1 ----
+// The boolean is order-independent, so classes are visited cheapest-first, except that the cubic class moves
+// in front of the sphere class while cubics are the more productive occluders per unit of work (block-local
+// statistics in WaveCtl::occ_found, updated as occluders are found).
 template <bool SEGMENT01>
-__device__ __forceinline__ int occluder_wave(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg,
+__device__ __forceinline__ int occluder_spheres(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg,
+                                                const d3 &o, const d3 &d, double max_t, Tally &tl)
+{
+    const int slot = g.n_plane;
+    const RayF rf = make_rayf(o, d, g.sphere_center_max, cfg.sphere_r2_max);
+    int found = -1;
+    const int n4 = rf.safe ? (g.n_sphere & ~3) : 0;
+    int i = 0;
+    for (; i < n4 && found < 0; i += 4) {
+        const float s0 = sphere_slack(rf, s.sphere_f[i]), s1 = sphere_slack(rf, s.sphere_f[i + 1]);
+        const float s2 = sphere_slack(rf, s.sphere_f[i + 2]), s3 = sphere_slack(rf, s.sphere_f[i + 3]);
+        if (!(fmaxf(fmaxf(s0, s1), fmaxf(s2, s3)) < 0.0f)) {
+#pragma unroll 1
+            for (int j = i; j < i + 4; j++) {
+                if (!sphere_rejected<SEGMENT01>(rf, s.sphere_f[j])) {
+                    tl.n[CNT_CONFIRM]++;
+                    if (blocks(intersect_sphere(g.sphere[j], o, d), max_t)) {
+                        found = slot + j;
+                        break;
+                    }
+                }
+            }
+        }
+    }
+    for (; i < g.n_sphere && found < 0; i++) {
+        if (!rf.safe || !sphere_rejected<SEGMENT01>(rf, s.sphere_f[i])) {
+            tl.n[CNT_CONFIRM]++;
+            if (blocks(intersect_sphere(g.sphere[i], o, d), max_t)) found = slot + i;
+        }
+    }
+    tl.n[CNT_T_SPHERE] += i;
+    return found;
+}
+
+__device__ __forceinline__ int occluder_cubics(const SceneView &g, const SceneSmem &s, const d3 &o, const d3 &d,
+                                               double max_t, Tally &tl)
+{
+    const int base = g.n_plane + g.n_sphere + g.n_quadric;
+    for (int i = 0; i < g.n_cubic; i++) {
+        tl.n[CNT_T_CUBIC]++;
+        if (blocks(intersect_cubic_masked(s.cubic + 20 * i, s.cubic_mask[i], o, d), max_t)) return base + i;
+    }
+    return -1;
+}
+
+template <bool SEGMENT01>
+__device__ __forceinline__ int occluder_wave(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg, WaveCtl &ctl,
                                              const d3 &o, const d3 &d, double max_t, Tally &tl)
 {
-    int slot = 0;
-    for (int i = 0; i < g.n_plane; i++, slot++) {
+    for (int i = 0; i < g.n_plane; i++) {
         tl.n[CNT_T_PLANE]++;
-        if (blocks(intersect_plane(s.plane[i], o, d), max_t)) return slot;
+        if (blocks(intersect_plane(s.plane[i], o, d), max_t)) return i;
     }
     const int quad_base = g.n_plane + g.n_sphere;
     for (int i = 0; i < g.n_quadric; i++) {
         tl.n[CNT_T_QUADRIC]++;
         if (blocks(intersect_quadric(s.quadric + 10 * i, o, d), max_t)) return quad_base + i;
     }
-    if (g.n_sphere > 0) {
-        const RayF rf = make_rayf(o, d, g.sphere_center_max, cfg.sphere_r2_max);
-        int found = -1;
-        int i = 0;
-#pragma unroll 4
-        for (; i < g.n_sphere; i++) {
-            if (!sphere_rejected<SEGMENT01>(rf, s.sphere_f[i])) {
-                tl.n[CNT_CONFIRM]++;
-                if (blocks(intersect_sphere(g.sphere[i], o, d), max_t)) {
-                    found = slot + i;
-                    i++;
-                    break;
-                }
-            }
-        }
-        tl.n[CNT_T_SPHERE] += i;
-        if (found >= 0) return found;
+    if (g.n_sphere == 0) return g.n_cubic ? occluder_cubics(g, s, o, d, max_t, tl) : -1;
+    if (g.n_cubic == 0) return occluder_spheres<SEGMENT01>(g, s, cfg, o, d, max_t, tl);
+    // relative cost of a full pass: ~4 issue slots x 4 per sphere filter, ~600 per exact cubic test
+    const volatile int *found = ctl.occ_found;
+    const bool cubic_first = (long long) found[1] * (16LL * g.n_sphere) > (long long) found[0] * (600LL * g.n_cubic);
+    int by = cubic_first ? occluder_cubics(g, s, o, d, max_t, tl) : occluder_spheres<SEGMENT01>(g, s, cfg, o, d, max_t, tl);
+    if (by >= 0) {
+        atomicAdd(&ctl.occ_found[cubic_first ? 1 : 0], 1);
+        return by;
     }
-    const int cubic_base = quad_base + g.n_quadric;
-    for (int i = 0; i < g.n_cubic; i++) {
-        tl.n[CNT_T_CUBIC]++;
-        if (blocks(intersect_cubic_masked(s.cubic + 20 * i, s.cubic_mask[i], o, d), max_t)) return cubic_base + i;
-    }
-    return -1;
+    by = cubic_first ? occluder_spheres<SEGMENT01>(g, s, cfg, o, d, max_t, tl) : occluder_cubics(g, s, o, d, max_t, tl);
+    if (by >= 0) atomicAdd(&ctl.occ_found[cubic_first ? 0 : 1], 1);
+    return by;
 }
 
 } // namespace

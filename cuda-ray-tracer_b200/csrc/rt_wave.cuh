@@ -45,6 +45,7 @@ struct WaveCtl {
     int tile;
     int warp_base[WAVE / 32];
     int shadow_cache[LIGHT_CHUNK];
+    int occ_found[2];            // occluders found so far by [0] the sphere pass, [1] the cubic pass
 };
 
 struct WaveConfig {

@@ -70,7 +70,10 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         LightDev *lt = reinterpret_cast<LightDev *>(sp);
         for (int i = tid; i < g.n_lights; i += WAVE) lt[i] = g.lights[i];
         s.lights = lt;
-        if (tid == 0) ctl.pool_count = 0;
+        if (tid == 0) {
+            ctl.pool_count = 0;
+            ctl.occ_found[0] = ctl.occ_found[1] = 0;
+        }
         if (tid < LIGHT_CHUNK) ctl.shadow_cache[tid] = -1;
     }
     __syncthreads();
@@ -203,8 +206,8 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
                     if (cs >= 0) occ = blocks(intersect_slot(g, s, cs, so, sd, tl), max_t);
                 }
                 if (!occ) {
-                    const int by = l.is_spherical ? occluder_wave<true>(g, s, cfg, so, sd, max_t, tl)
-                                                  : occluder_wave<false>(g, s, cfg, so, sd, max_t, tl);
+                    const int by = l.is_spherical ? occluder_wave<true>(g, s, cfg, ctl, so, sd, max_t, tl)
+                                                  : occluder_wave<false>(g, s, cfg, ctl, so, sd, max_t, tl);
                     occ = by >= 0;
                     if (occ && cfg.use_shadow_cache) ctl.shadow_cache[j] = by;   // benign race: any occluder will do
                 }
