@@ -119,6 +119,7 @@ struct rt_b200_ctx {
     unsigned *d_cubic_mask = nullptr;
     float sphere_r2_max = 0.0f;
     int shadow_cache = -1;
+    int wave_variant = 0;
     bool buffers_dirty = true;
 
     int kernel_kind = 1;
@@ -366,7 +367,7 @@ int rt_b200_update(rt_b200_ctx *c, const double camera_matrix[16], float *elapse
         CUDA_TRY(rt::launch_render_exact(c->view, f, c->stream));
     }
     else {
-        rt::WaveLaunch wl{c->d_tile_counter, c->d_cubic_mask, c->sphere_r2_max, c->shadow_cache};
+        rt::WaveLaunch wl{c->d_tile_counter, c->d_cubic_mask, c->sphere_r2_max, c->shadow_cache, c->wave_variant};
         CUDA_TRY(rt::launch_render_wave(c->view, f, wl, c->stream));
     }
     CUDA_TRY(cudaEventRecord(c->ev_render, c->stream));
@@ -491,6 +492,10 @@ int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
             c->strip_rows = (int) value;
             c->buffers_dirty = true;
         }
+    }
+    else if (!std::strcmp(name, "variant")) {
+        if (value < 0 || value > 5) return fail(RT_B200_ERR_ARG, "variant must be 0..5");
+        c->wave_variant = (int) value;
     }
     else if (!std::strcmp(name, "shadow_cache")) {
         if (value < -1 || value > 1) return fail(RT_B200_ERR_ARG, "shadow_cache must be -1, 0 or 1");

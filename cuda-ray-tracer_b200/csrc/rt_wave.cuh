@@ -8,9 +8,8 @@
 
 namespace rt {
 
-constexpr int WAVE = 256;        // threads per CTA == rays per wave
-constexpr int POOL_CAP = 2 * WAVE;
 constexpr int LIGHT_CHUNK = 32;  // lights handled per visibility word
+constexpr int MAX_WARPS = 16;    // largest CTA: 512 threads
 
 // Scene arrays staged once per CTA into shared memory (SoA by class, rt_scene.h).
 struct SceneSmem {
@@ -22,34 +21,37 @@ struct SceneSmem {
     const LightDev *lights;
 };
 
-// Ray pool: reflection rays waiting for a full wave (block-local, never leaves the SM).
+// Ray pool: reflection rays waiting for a full wave (block-local, never leaves the SM).  W = threads per CTA
+// = rays per wave; capacity 2 W (a wave is taken as soon as W rays wait, and adds at most W).
+template <int W>
 struct Pool {
-    double ox[POOL_CAP], oy[POOL_CAP], oz[POOL_CAP];
-    double dx[POOL_CAP], dy[POOL_CAP], dz[POOL_CAP];
-    float out_r[POOL_CAP], out_g[POOL_CAP], out_b[POOL_CAP], ratio[POOL_CAP];
-    int pixel[POOL_CAP];
-    int bounces[POOL_CAP];
+    double ox[2 * W], oy[2 * W], oz[2 * W];
+    double dx[2 * W], dy[2 * W], dz[2 * W];
+    float out_r[2 * W], out_g[2 * W], out_b[2 * W], ratio[2 * W];
+    int pixel[2 * W];
+    int bounces[2 * W];
 };
 
 // Per-wave hit records (indexed by wave slot, not compacted: only the index list is).
+template <int W>
 struct WaveHits {
-    double px[WAVE], py[WAVE], pz[WAVE];
-    double nx[WAVE], ny[WAVE], nz[WAVE];
-    unsigned occluded[WAVE];     // bit j: light (chunk base + j) is shadowed
-    unsigned short hitlist[WAVE];
+    double px[W], py[W], pz[W];
+    double nx[W], ny[W], nz[W];
+    unsigned occluded[W];        // bit j: light (chunk base + j) is shadowed
+    unsigned short hitlist[W];
 };
 
 struct WaveCtl {
     int pool_count;
     int n_hits;
     int tile;
-    int warp_base[WAVE / 32];
+    int warp_base[MAX_WARPS];
     int shadow_cache[LIGHT_CHUNK];
     int occ_found[2];            // occluders found so far by [0] the sphere pass, [1] the cubic pass
 };
 
 struct WaveConfig {
-    int tiles_x, tiles_y;        // 32x8 pixel tiles over [local_rows][width]
+    int tiles_x, tiles_y;        // 32 x (W/32) pixel tiles over [local_rows][width]
     int spheres_in_smem;
     int use_shadow_cache;
     unsigned long long *tile_counter;
@@ -60,7 +62,11 @@ struct WaveConfig {
 __host__ __device__ inline size_t align16(size_t v) { return (v + 15) & ~(size_t) 15; }
 
 // dynamic shared memory: [Pool][WaveHits][WaveCtl][scene arrays...]
-__host__ __device__ inline size_t wave_fixed_smem() { return align16(sizeof(Pool)) + align16(sizeof(WaveHits)) + align16(sizeof(WaveCtl)); }
+template <int W>
+__host__ __device__ inline size_t wave_fixed_smem()
+{
+    return align16(sizeof(Pool<W>)) + align16(sizeof(WaveHits<W>)) + align16(sizeof(WaveCtl));
+}
 
 __host__ __device__ inline size_t wave_scene_smem(const SceneView &sc, bool spheres)
 {

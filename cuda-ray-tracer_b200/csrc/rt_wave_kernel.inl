@@ -26,16 +26,18 @@ __device__ __forceinline__ float blend(float out, float ratio, float c) { return
 
 } // namespace
 
-template <bool COUNT>
-__global__ void __launch_bounds__(WAVE, 2)
+template <int W, int MINB, bool COUNT>
+__global__ void __launch_bounds__(W, MINB)
 render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ FrameParams f,
                    const __grid_constant__ WaveConfig cfg)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    Pool &pool = *reinterpret_cast<Pool *>(smem_raw);
-    WaveHits &wh = *reinterpret_cast<WaveHits *>(smem_raw + align16(sizeof(Pool)));
-    WaveCtl &ctl = *reinterpret_cast<WaveCtl *>(smem_raw + align16(sizeof(Pool)) + align16(sizeof(WaveHits)));
-    unsigned char *sp = smem_raw + wave_fixed_smem();
+    constexpr int WAVE = W;
+    constexpr int TILE_ROWS = W / 32;            // tile = 32 x TILE_ROWS pixels, an 8x4 sub-tile per warp
+    Pool<W> &pool = *reinterpret_cast<Pool<W> *>(smem_raw);
+    WaveHits<W> &wh = *reinterpret_cast<WaveHits<W> *>(smem_raw + align16(sizeof(Pool<W>)));
+    WaveCtl &ctl = *reinterpret_cast<WaveCtl *>(smem_raw + align16(sizeof(Pool<W>)) + align16(sizeof(WaveHits<W>)));
+    unsigned char *sp = smem_raw + wave_fixed_smem<W>();
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
@@ -119,7 +121,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         if (primary) {
             const int tx = tile % cfg.tiles_x, ty = tile / cfg.tiles_x;
             const int x = tx * 32 + (warp & 3) * 8 + (lane & 7);
-            const int lrow = ty * 8 + (warp >> 2) * 4 + (lane >> 3);
+            const int lrow = ty * TILE_ROWS + (warp >> 2) * 4 + (lane >> 3);
             const int y = local_to_image_row(lrow, f.strip_rows, f.rank, f.world);
             const bool in_buf = x < f.width && lrow < f.local_rows;
             active = in_buf && y < f.height;
@@ -284,50 +286,76 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
     if (COUNT) flush_tally(tl, f.counters);
 }
 
-static size_t g_wave_smem_limit = 0;
+namespace {
 
+template <int W, int MINB>
+cudaError_t launch_wave_variant(const SceneView &scene, const FrameParams &frame, WaveConfig cfg, size_t scene_smem,
+                                int n_sm, int max_smem, cudaStream_t stream)
+{
+    static bool attr_set = false;
+    auto kern = frame.counters ? render_wave_kernel<W, MINB, true> : render_wave_kernel<W, MINB, false>;
+    cudaError_t e;
+    if (!attr_set) {
+        e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    const size_t smem = wave_fixed_smem<W>() + scene_smem;
+    cfg.tiles_x = (frame.width + 31) / 32;
+    cfg.tiles_y = (frame.local_rows + W / 32 - 1) / (W / 32);
+    int per_sm = 1;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W, smem);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) return cudaErrorInvalidConfiguration;
+    const int n_tiles = cfg.tiles_x * cfg.tiles_y;
+    int grid = n_sm * per_sm;
+    if (grid > n_tiles) grid = n_tiles;
+    e = cudaMemsetAsync(cfg.tile_counter, 0, sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
+    kern<<<grid, W, smem, stream>>>(scene, frame, cfg);
+    return cudaGetLastError();
+}
+
+} // namespace
+
+// Variant choice: 256-thread CTAs, two (or three) per SM, while the staged scene leaves room for that; otherwise
+// one 512-thread CTA per SM so that a large scene is staged once and still 16 warps are resident.
 cudaError_t launch_render_wave(const SceneView &scene, const FrameParams &frame, const WaveLaunch &wl, cudaStream_t stream)
 {
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
-    int n_sm = 0, max_smem = 0;
+    int n_sm = 0, max_smem = 0, sm_smem = 0;
     cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
     cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    cudaDeviceGetAttribute(&sm_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
 
     WaveConfig cfg;
-    cfg.tiles_x = (frame.width + 31) / 32;
-    cfg.tiles_y = (frame.local_rows + 7) / 8;
+    cfg.tiles_x = cfg.tiles_y = 0;
     cfg.tile_counter = wl.tile_counter;
     cfg.cubic_mask = wl.cubic_mask;
     cfg.sphere_r2_max = wl.sphere_r2_max;
     cfg.use_shadow_cache = wl.shadow_cache >= 0 ? wl.shadow_cache : (scene.n_objects >= 8 ? 1 : 0);
-    size_t smem = wave_fixed_smem() + wave_scene_smem(scene, true);
     cfg.spheres_in_smem = 1;
-    if (smem > (size_t) max_smem) {
+    size_t scene_smem = wave_scene_smem(scene, true);
+    if (wave_fixed_smem<512>() + scene_smem > (size_t) max_smem) {
         cfg.spheres_in_smem = 0;
-        smem = wave_fixed_smem() + wave_scene_smem(scene, false);
-        if (smem > (size_t) max_smem) return cudaErrorInvalidConfiguration;
+        scene_smem = wave_scene_smem(scene, false);
+        if (wave_fixed_smem<256>() + scene_smem > (size_t) max_smem) return cudaErrorInvalidConfiguration;
     }
-    auto kern = frame.counters ? render_wave_kernel<true> : render_wave_kernel<false>;
-    if (smem > g_wave_smem_limit) {
-        e = cudaFuncSetAttribute(render_wave_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(render_wave_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
-        if (e != cudaSuccess) return e;
-        g_wave_smem_limit = (size_t) max_smem;
+    const size_t cta256 = wave_fixed_smem<256>() + scene_smem + 1024;   // + per-CTA reservation
+    int variant = wl.variant;
+    if (variant <= 0) variant = (3 * cta256 <= (size_t) sm_smem) ? 3 : 5;
+    switch (variant) {
+        case 1: return launch_wave_variant<256, 1>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
+        case 2: return launch_wave_variant<256, 2>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
+        case 3: return launch_wave_variant<256, 3>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
+        case 4: return launch_wave_variant<256, 4>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
+        case 5: return launch_wave_variant<512, 1>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
+        default: return cudaErrorInvalidValue;
     }
-    int per_sm = 1;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, WAVE, smem);
-    if (e != cudaSuccess) return e;
-    if (per_sm < 1) per_sm = 1;
-    const int n_tiles = cfg.tiles_x * cfg.tiles_y;
-    int grid = n_sm * per_sm;
-    if (grid > n_tiles) grid = n_tiles;
-    e = cudaMemsetAsync(wl.tile_counter, 0, sizeof(unsigned long long), stream);
-    if (e != cudaSuccess) return e;
-    kern<<<grid, WAVE, smem, stream>>>(scene, frame, cfg);
-    return cudaGetLastError();
 }
 
 } // namespace rt
