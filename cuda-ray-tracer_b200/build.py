@@ -15,7 +15,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "librt_b200.so")
-SOURCES = ["rt_api.cu", "rt_kernels.cu", "rt_wave.cu"]
+SOURCES = ["rt_api.cu", "rt_kernels.cu", "rt_wave.cu", "rt_queue.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall", "--use_fast_math=false"]
 

@@ -20,6 +20,7 @@
 
 #include "../../include/rt_b200.h"
 #include "rt_kernels.h"
+#include "rt_tables.cuh"
 
 namespace {
 
@@ -117,6 +118,9 @@ struct rt_b200_ctx {
     unsigned long long *d_counters = nullptr;
     unsigned long long *d_tile_counter = nullptr;
     unsigned *d_cubic_mask = nullptr;
+    std::vector<unsigned> cubic_mask_host;
+    rt::QueueTables qtables{};       // queue kernel: FP32 sphere tables (rt_tables.cuh)
+    int queue_variant = 0, queue_cap_mult = 0;
     float sphere_r2_max = 0.0f;
     int shadow_cache = -1;
     int wave_variant = 0;
@@ -226,7 +230,8 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     std::vector<double> quadric, cubic, coef_full(20 * n_objects);
     std::vector<int> orig[4];
     std::vector<unsigned> cubic_mask;
-    float center_max = 0.0f, r2_max = 0.0f;
+    float center_max = 0.0f, r2_max = 0.0f, center_norm_max = 0.0f;
+    bool tables_safe = true;   // FP32 tables need |coordinates| < 1e9, r^2 < 1e18 (NaN counts as unsafe)
     const char *obj_bytes = static_cast<const char *>(objects);
     for (size_t i = 0; i < n_objects; i++) {
         double k[20];
@@ -250,6 +255,8 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
                 sphere_f.push_back(make_float4((float) cx, (float) cy, (float) cz, (float) r2));
                 r2_max = fmaxf(r2_max, nextafterf((float) fabs(r2), INFINITY));
                 center_max = fmaxf(center_max, fmaxf(fabsf((float) cx), fmaxf(fabsf((float) cy), fabsf((float) cz))));
+                center_norm_max = fmaxf(center_norm_max, nextafterf((float) sqrt(cx * cx + cy * cy + cz * cz), INFINITY));
+                if (!(fabs(cx) < 1e9 && fabs(cy) < 1e9 && fabs(cz) < 1e9 && fabs(r2) < 1e18)) tables_safe = false;
                 break;
             }
             case rt::CLS_QUADRIC:
@@ -280,6 +287,7 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
         std::memcpy(p, rec + 8, 24);
         std::memcpy(col, rec + 32, 12);
         ldev[j] = rt::LightDev{p[0], p[1], p[2], col[0], col[1], col[2], rec[0] != 0 ? 1 : 0};
+        if (!(fabs(p[0]) < 1e9 && fabs(p[1]) < 1e9 && fabs(p[2]) < 1e9)) tables_safe = false;
     }
 
     int rc = RT_B200_OK;
@@ -298,6 +306,17 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     up(upload(cubic_mask, &c->d_cubic_mask), "cubic masks");
     up(cudaMalloc((void **) &c->d_tile_counter, sizeof(unsigned long long)), "tile counter");
     c->sphere_r2_max = r2_max;
+    c->cubic_mask_host = cubic_mask;
+    // queue kernel tables: [2 + n_lights] rows of n_sphere_pad entries
+    c->qtables.n_sphere_pad = ((int) sphere.size() + 3) & ~3;
+    c->qtables.r2_max = r2_max;
+    c->qtables.r_max = nextafterf(sqrtf(r2_max), INFINITY);
+    c->qtables.center_norm_max = center_norm_max;
+    c->qtables.tables_safe = tables_safe ? 1 : 0;
+    up(cudaMalloc((void **) &c->qtables.tables,
+                  sizeof(float4) * (size_t) (2 + n_lights) * (c->qtables.n_sphere_pad ? c->qtables.n_sphere_pad : 4)),
+       "sphere tables");
+    up(cudaMalloc((void **) &c->qtables.light_filter, sizeof(rt::LightFilter) * (n_lights ? n_lights : 1)), "light filters");
     up(cudaMalloc((void **) &c->d_counters, sizeof(unsigned long long) * rt::CNT_COUNT), "counters");
     up(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "stream");
     up(cudaEventCreate(&c->ev_start), "event");
@@ -328,6 +347,15 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     v.sphere_center_max = center_max;
 
     rc = ensure_buffers(c);
+    if (rc == RT_B200_OK) {
+        // light families and every table row that does not depend on the camera (rows 0 and 2..)
+        const double zero[3] = {0.0, 0.0, 0.0};
+        cudaError_t e = rt::build_light_filters(v, c->qtables, c->stream);
+        if (e == cudaSuccess) e = rt::build_queue_tables(v, c->qtables, 0, 1, zero, c->stream);
+        if (e == cudaSuccess) e = rt::build_queue_tables(v, c->qtables, 2, 2 + v.n_lights, zero, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) rc = fail(RT_B200_ERR_CUDA, "sphere tables: %s", cudaGetErrorString(e));
+    }
     if (rc != RT_B200_OK) {
         rt_b200_destroy(c);
         return rc;
@@ -365,6 +393,21 @@ int rt_b200_update(rt_b200_ctx *c, const double camera_matrix[16], float *elapse
     CUDA_TRY(cudaEventRecord(c->ev_start, c->stream));
     if (c->kernel_kind == 0) {
         CUDA_TRY(rt::launch_render_exact(c->view, f, c->stream));
+    }
+    else if (c->kernel_kind == 2) {
+        // the primary-ray table depends on the camera origin: one small setup launch per frame
+        CUDA_TRY(rt::build_queue_tables(c->view, c->qtables, 1, 2, f.origin, c->stream));
+        rt::QueueLaunch ql{};
+        ql.tile_counter = c->d_tile_counter;
+        ql.tables = c->qtables;
+        ql.cubic_mask_host = c->cubic_mask_host.data();
+        ql.n_masks = (int) c->cubic_mask_host.size();
+        ql.primary_safe = (fabs(f.origin[0]) < 1e9 && fabs(f.origin[1]) < 1e9 && fabs(f.origin[2]) < 1e9) ? 1 : 0;
+        ql.shadow_cache = c->shadow_cache;
+        ql.variant = c->queue_variant;
+        ql.cap_mult = c->queue_cap_mult;
+        ql.direct = 0;
+        CUDA_TRY(rt::launch_render_queue(c->view, f, ql, c->stream));
     }
     else {
         rt::WaveLaunch wl{c->d_tile_counter, c->d_cubic_mask, c->sphere_r2_max, c->shadow_cache, c->wave_variant};
@@ -437,6 +480,8 @@ int rt_b200_destroy(rt_b200_ctx *c)
     cudaFree(c->d_counters);
     cudaFree(c->d_tile_counter);
     cudaFree(c->d_cubic_mask);
+    cudaFree(c->qtables.tables);
+    cudaFree(c->qtables.light_filter);
     if (c->ev_start) cudaEventDestroy(c->ev_start);
     if (c->ev_render) cudaEventDestroy(c->ev_render);
     if (c->ev_end) cudaEventDestroy(c->ev_end);
@@ -483,7 +528,7 @@ int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
 {
     if (!c || !name) return fail(RT_B200_ERR_ARG, "null argument");
     if (!std::strcmp(name, "kernel")) {
-        if (value < 0 || value > 1) return fail(RT_B200_ERR_ARG, "kernel must be 0 or 1");
+        if (value < 0 || value > 2) return fail(RT_B200_ERR_ARG, "kernel must be 0, 1 or 2");
         c->kernel_kind = (int) value;
     }
     else if (!std::strcmp(name, "strip_rows")) {
@@ -496,6 +541,14 @@ int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
     else if (!std::strcmp(name, "variant")) {
         if (value < 0 || value > 5) return fail(RT_B200_ERR_ARG, "variant must be 0..5");
         c->wave_variant = (int) value;
+    }
+    else if (!std::strcmp(name, "queue_variant")) {
+        if (value < 0 || value > 4) return fail(RT_B200_ERR_ARG, "queue_variant must be 0..4");
+        c->queue_variant = (int) value;
+    }
+    else if (!std::strcmp(name, "queue_cap")) {
+        if (value != 0 && (value < 2 || value > 8)) return fail(RT_B200_ERR_ARG, "queue_cap must be 0 or 2..8");
+        c->queue_cap_mult = (int) value;
     }
     else if (!std::strcmp(name, "shadow_cache")) {
         if (value < -1 || value > 1) return fail(RT_B200_ERR_ARG, "shadow_cache must be -1, 0 or 1");

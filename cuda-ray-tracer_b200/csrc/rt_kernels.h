@@ -19,6 +19,33 @@ struct WaveLaunch {
 };
 cudaError_t launch_render_wave(const SceneView &scene, const FrameParams &frame, const WaveLaunch &wl, cudaStream_t stream);
 
+// Queue kernel (rt_queue.cu): per-scene / per-frame FP32 sphere tables (rt_tables.cuh) and the launcher.
+struct LightFilter;
+struct QueueTables {
+    float4 *tables;              // device, [2 + n_lights][n_sphere_pad]: 0 generic, 1 primary (per frame), 2 + j light j
+    LightFilter *light_filter;   // device, [n_lights]
+    int n_sphere_pad;            // n_sphere rounded up to a multiple of 4
+    int tables_safe;             // all sphere / light coordinates small enough for FP32 tables
+    float r_max, r2_max, center_norm_max;
+};
+struct QueueLaunch {
+    unsigned long long *tile_counter;
+    QueueTables tables;
+    const unsigned *cubic_mask_host;    // host, [n_masks]
+    int n_masks;
+    int primary_safe;                   // camera origin small enough for the FP32 primary table
+    int shadow_cache;                   // 1 / 0 / -1 = automatic
+    int variant;                        // 0 = automatic; 1: 256 threads, tables resident; 2: 512 threads, streamed;
+                                        // 3: 512 threads, resident; 4: 256 threads, streamed
+    int cap_mult;                       // path records per CTA = cap_mult * threads (0 = default 3)
+    int direct;                         // pixels go to their image position (frame shared across GPUs)
+};
+cudaError_t build_light_filters(const SceneView &scene, const QueueTables &qt, cudaStream_t stream);
+// Rows [row_begin, row_end) of the table set; `pivot` = camera origin (used by row 1 only).
+cudaError_t build_queue_tables(const SceneView &scene, const QueueTables &qt, int row_begin, int row_end,
+                               const double pivot[3], cudaStream_t stream);
+cudaError_t launch_render_queue(const SceneView &scene, const FrameParams &frame, const QueueLaunch &ql, cudaStream_t stream);
+
 // Undo the strip interleave after the all-gather: gathered = [world][local_rows][width] -> frame[height][width].
 cudaError_t launch_unpack_strips(const uchar4 *gathered, uchar4 *frame, int width, int height, int strip_rows,
                                  int world, int local_rows, cudaStream_t stream);

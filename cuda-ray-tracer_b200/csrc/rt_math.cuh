@@ -55,7 +55,7 @@ __device__ __forceinline__ double solve_quadratic_or_linear(double t2, double t1
     return -1.0;
 }
 
-static __device__ __noinline__ double solve_cubic(double t3, double t2, double t1, double t0)
+__device__ __forceinline__ double solve_cubic_inline(double t3, double t2, double t1, double t0)
 {
     t2 /= t3;
     t1 /= t3;
@@ -77,6 +77,19 @@ static __device__ __noinline__ double solve_cubic(double t3, double t2, double t
     x1 = c * cos(theta + 2.0 * RT_TWO_THIRD_PI) - t2 / 3.0;
     if (x1 >= RT_EPS && x1 < x) x = x1;
     return x;
+}
+
+// out-of-line copy for kernels that call the solver from many places (exact and wavefront kernels)
+static __device__ __noinline__ double solve_cubic(double t3, double t2, double t1, double t0)
+{
+    return solve_cubic_inline(t3, t2, t1, t0);
+}
+
+// fully inlined: for kernels with a single solver call site (queue kernel)
+__device__ __forceinline__ double solve_poly_inline(const Poly &p)
+{
+    if (fabs(p.t3) > RT_EPS) return solve_cubic_inline(p.t3, p.t2, p.t1, p.t0);
+    return solve_quadratic_or_linear(p.t2, p.t1, p.t0);
 }
 
 __device__ __forceinline__ double solve_poly(const Poly &p)
@@ -104,6 +117,21 @@ __device__ __forceinline__ double intersect_sphere(const double4 k, const d3 &o,
 }
 
 // q = {x2,y2,z2,xy,xz,yz,x,y,z,c}
+__device__ __forceinline__ Poly expand_quadric(const double *__restrict__ q, const d3 &o, const d3 &d)
+{
+    Poly p;
+    p.t3 = 0.0;
+    p.t2 = q[0] * (d.x * d.x) + q[1] * (d.y * d.y) + q[2] * (d.z * d.z)
+           + q[3] * (d.x * d.y) + q[4] * (d.x * d.z) + q[5] * (d.y * d.z);
+    p.t1 = q[0] * (2.0 * o.x * d.x) + q[1] * (2.0 * o.y * d.y) + q[2] * (2.0 * o.z * d.z)
+           + q[3] * (o.x * d.y + d.x * o.y) + q[4] * (o.x * d.z + d.x * o.z) + q[5] * (o.y * d.z + d.y * o.z)
+           + q[6] * d.x + q[7] * d.y + q[8] * d.z;
+    p.t0 = q[0] * (o.x * o.x) + q[1] * (o.y * o.y) + q[2] * (o.z * o.z)
+           + q[3] * (o.x * o.y) + q[4] * (o.x * o.z) + q[5] * (o.y * o.z)
+           + q[6] * o.x + q[7] * o.y + q[8] * o.z + q[9];
+    return p;
+}
+
 __device__ __forceinline__ double intersect_quadric(const double *__restrict__ q, const d3 &o, const d3 &d)
 {
     double t2 = q[0] * (d.x * d.x) + q[1] * (d.y * d.y) + q[2] * (d.z * d.z)

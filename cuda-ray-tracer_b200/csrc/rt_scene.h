@@ -76,5 +76,7 @@ __host__ __device__ inline int local_to_image_row(int local_row, int strip_rows,
     return (s_local * world + rank) * strip_rows + r;
 }
 
+__host__ __device__ inline size_t align16(size_t v) { return (v + 15) & ~(size_t) 15; }
+
 } // namespace rt
 #endif

@@ -49,6 +49,21 @@ __device__ __forceinline__ void consider_lazy(Hit &h, double t, int slot, const 
     }
 }
 
+// The same rule on two scalars (queue kernel).
+__device__ __forceinline__ void consider_lazy_t(double &best_t, int &best_slot, double t, int slot,
+                                                const int *__restrict__ orig_index)
+{
+    if (t >= RT_EPS && t < RT_MAX_T) {
+        if (t < best_t) {
+            best_t = t;
+            best_slot = slot;
+        }
+        else if (t == best_t && best_slot >= 0 && __ldg(&orig_index[slot]) < __ldg(&orig_index[best_slot])) {
+            best_slot = slot;
+        }
+    }
+}
+
 __device__ __forceinline__ Hit nearest_hit_exact(const SceneView &sc, const d3 &o, const d3 &d, Tally &tl)
 {
     Hit h;

@@ -59,8 +59,6 @@ struct WaveConfig {
     float sphere_r2_max;
 };
 
-__host__ __device__ inline size_t align16(size_t v) { return (v + 15) & ~(size_t) 15; }
-
 // dynamic shared memory: [Pool][WaveHits][WaveCtl][scene arrays...]
 template <int W>
 __host__ __device__ inline size_t wave_fixed_smem()
