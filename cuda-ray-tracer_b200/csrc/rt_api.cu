@@ -20,7 +20,7 @@
 
 #include "../../include/rt_b200.h"
 #include "rt_kernels.h"
-#include "rt_tables.cuh"
+#include "rt_queue.cuh"
 
 namespace {
 
@@ -118,9 +118,9 @@ struct rt_b200_ctx {
     unsigned long long *d_counters = nullptr;
     unsigned long long *d_tile_counter = nullptr;
     unsigned *d_cubic_mask = nullptr;
-    std::vector<unsigned> cubic_mask_host;
     rt::QueueTables qtables{};       // queue kernel: FP32 sphere tables (rt_tables.cuh)
-    int queue_variant = 0, queue_cap_mult = 0;
+    rt::QueueScene *qscene = nullptr;   // queue kernel: scene block passed in the kernel parameters (null: does not fit)
+    int queue_variant = 0;
     float sphere_r2_max = 0.0f;
     int shadow_cache = -1;
     int wave_variant = 0;
@@ -306,7 +306,6 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     up(upload(cubic_mask, &c->d_cubic_mask), "cubic masks");
     up(cudaMalloc((void **) &c->d_tile_counter, sizeof(unsigned long long)), "tile counter");
     c->sphere_r2_max = r2_max;
-    c->cubic_mask_host = cubic_mask;
     // queue kernel tables: [2 + n_lights] rows of n_sphere_pad entries
     c->qtables.n_sphere_pad = ((int) sphere.size() + 3) & ~3;
     c->qtables.r2_max = r2_max;
@@ -316,7 +315,21 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     up(cudaMalloc((void **) &c->qtables.tables,
                   sizeof(float4) * (size_t) (2 + n_lights) * (c->qtables.n_sphere_pad ? c->qtables.n_sphere_pad : 4)),
        "sphere tables");
-    up(cudaMalloc((void **) &c->qtables.light_filter, sizeof(rt::LightFilter) * (n_lights ? n_lights : 1)), "light filters");
+    // queue kernel scene block (kernel parameters): everything except the spheres
+    if (plane.size() <= rt::QK_MAX_PLANE && quadric.size() <= 10 * (size_t) rt::QK_MAX_QUADRIC &&
+        cubic_mask.size() <= rt::QK_MAX_CUBIC && n_lights <= (size_t) rt::QK_MAX_LIGHT) {
+        rt::QueueScene *qs = new rt::QueueScene();
+        std::memset(qs, 0, sizeof(*qs));
+        for (size_t i = 0; i < plane.size(); i++) qs->plane[i] = plane[i];
+        for (size_t i = 0; i < quadric.size(); i++) qs->quadric[i / 10][i % 10] = quadric[i];
+        for (size_t i = 0; i < cubic.size(); i++) qs->cubic[i / 20][i % 20] = cubic[i];
+        for (size_t i = 0; i < cubic_mask.size(); i++) qs->cubic_mask[i] = cubic_mask[i];
+        for (size_t j = 0; j < n_lights; j++) {
+            qs->light[j] = ldev[j];
+            qs->lf[j] = rt::make_light_filter(ldev[j]);
+        }
+        c->qscene = qs;
+    }
     up(cudaMalloc((void **) &c->d_counters, sizeof(unsigned long long) * rt::CNT_COUNT), "counters");
     up(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "stream");
     up(cudaEventCreate(&c->ev_start), "event");
@@ -350,9 +363,11 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     if (rc == RT_B200_OK) {
         // light families and every table row that does not depend on the camera (rows 0 and 2..)
         const double zero[3] = {0.0, 0.0, 0.0};
-        cudaError_t e = rt::build_light_filters(v, c->qtables, c->stream);
-        if (e == cudaSuccess) e = rt::build_queue_tables(v, c->qtables, 0, 1, zero, c->stream);
-        if (e == cudaSuccess) e = rt::build_queue_tables(v, c->qtables, 2, 2 + v.n_lights, zero, c->stream);
+        cudaError_t e = cudaSuccess;
+        if (c->qscene) {
+            e = rt::build_queue_tables(v, c->qtables, *c->qscene, 0, 1, zero, c->stream);
+            if (e == cudaSuccess) e = rt::build_queue_tables(v, c->qtables, *c->qscene, 2, 2 + v.n_lights, zero, c->stream);
+        }
         if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
         if (e != cudaSuccess) rc = fail(RT_B200_ERR_CUDA, "sphere tables: %s", cudaGetErrorString(e));
     }
@@ -394,18 +409,16 @@ int rt_b200_update(rt_b200_ctx *c, const double camera_matrix[16], float *elapse
     if (c->kernel_kind == 0) {
         CUDA_TRY(rt::launch_render_exact(c->view, f, c->stream));
     }
-    else if (c->kernel_kind == 2) {
+    else if (c->kernel_kind == 2 && c->qscene) {
         // the primary-ray table depends on the camera origin: one small setup launch per frame
-        CUDA_TRY(rt::build_queue_tables(c->view, c->qtables, 1, 2, f.origin, c->stream));
+        CUDA_TRY(rt::build_queue_tables(c->view, c->qtables, *c->qscene, 1, 2, f.origin, c->stream));
         rt::QueueLaunch ql{};
         ql.tile_counter = c->d_tile_counter;
         ql.tables = c->qtables;
-        ql.cubic_mask_host = c->cubic_mask_host.data();
-        ql.n_masks = (int) c->cubic_mask_host.size();
+        ql.scene = c->qscene;
         ql.primary_safe = (fabs(f.origin[0]) < 1e9 && fabs(f.origin[1]) < 1e9 && fabs(f.origin[2]) < 1e9) ? 1 : 0;
         ql.shadow_cache = c->shadow_cache;
         ql.variant = c->queue_variant;
-        ql.cap_mult = c->queue_cap_mult;
         ql.direct = 0;
         CUDA_TRY(rt::launch_render_queue(c->view, f, ql, c->stream));
     }
@@ -481,7 +494,7 @@ int rt_b200_destroy(rt_b200_ctx *c)
     cudaFree(c->d_tile_counter);
     cudaFree(c->d_cubic_mask);
     cudaFree(c->qtables.tables);
-    cudaFree(c->qtables.light_filter);
+    delete c->qscene;
     if (c->ev_start) cudaEventDestroy(c->ev_start);
     if (c->ev_render) cudaEventDestroy(c->ev_render);
     if (c->ev_end) cudaEventDestroy(c->ev_end);
@@ -543,12 +556,8 @@ int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
         c->wave_variant = (int) value;
     }
     else if (!std::strcmp(name, "queue_variant")) {
-        if (value < 0 || value > 4) return fail(RT_B200_ERR_ARG, "queue_variant must be 0..4");
+        if (value < 0 || value > 5) return fail(RT_B200_ERR_ARG, "queue_variant must be 0..5");
         c->queue_variant = (int) value;
-    }
-    else if (!std::strcmp(name, "queue_cap")) {
-        if (value != 0 && (value < 2 || value > 8)) return fail(RT_B200_ERR_ARG, "queue_cap must be 0 or 2..8");
-        c->queue_cap_mult = (int) value;
     }
     else if (!std::strcmp(name, "shadow_cache")) {
         if (value < -1 || value > 1) return fail(RT_B200_ERR_ARG, "shadow_cache must be -1, 0 or 1");

@@ -42,6 +42,8 @@ enum FilterKind { FK_GENERIC = 0, FK_PIVOT = 1, FK_DIRECTION = 2 };
 struct LightFilter {
     double ux, uy, uz;   // FK_DIRECTION: orthonormal pair normal to the light direction
     double vx, vy, vz;
+    double sx, sy, sz;   // directional lights: the shadow direction exactly as shadow_ray() returns it
+                         // (rounded to float and widened, light_impl.h:24-25) — the same for every hit point
     int kind;            // FilterKind; FK_GENERIC when the light's data is unusable for a table (zero / huge vectors)
     int pad;
 };

@@ -15,7 +15,7 @@ ap.add_argument("--width", type=int, default=3840)
 ap.add_argument("--height", type=int, default=2160)
 ap.add_argument("--synth", default="960x540")
 ap.add_argument("--poses", default="initial,pose_a")
-ap.add_argument("--cap", type=int, default=0)
+ap.add_argument("--cap", type=int, default=0)  # unused
 a = ap.parse_args()
 todo = [(n, pkg.load_from_file(os.path.join(ROOT, "scenes", n + ".yml")).with_overrides(width=a.width, height=a.height, max_reflections=4))
         for n in a.scenes.split(",") if n]
@@ -35,8 +35,6 @@ for name, sc in todo:
             r.set_option("kernel", 1)
             row["wave_ms"] = round(min(r.update(m) for _ in range(3)), 4)
             r.set_option("kernel", 2)
-            if a.cap:
-                r.set_option("queue_cap", a.cap)
             for v in (int(x) for x in a.variants.split(",")):
                 r.set_option("queue_variant", v)
                 try:
