@@ -154,7 +154,7 @@ def run_reference(args):
     scenes, desc = build_workload(pkg, args.workload)
     cores = os.cpu_count() or 1
     kind = "reference" if oracle_py.have_ref() else "port"
-    ystep = args.ref_row_step
+    ystep = args.ref_row_step or 2
     m = camera.TEST_POSES["initial"]
     # ray census of the sampled rows (untimed, via the counting restatement)
     rays_sample = 0
@@ -217,6 +217,7 @@ def run_b200(args):
     scenes, desc = build_workload(pkg, args.workload)
     m = np.ascontiguousarray(camera.TEST_POSES["initial"])
     renderers = []
+    fused = world > 1 and args.gather == "p2p"
     for label, sc in scenes:
         r = binding.Renderer(sc, device=local, rank=rank, world_size=world)
         r.set_option("kernel", args.kernel)
@@ -225,36 +226,55 @@ def run_b200(args):
             ident = [binding.comm_unique_id() if rank == 0 else None]
             dist.broadcast_object_list(ident, src=0)
             r.comm_init(ident[0])
+            if fused:   # every rank's kernel stores its pixels straight into rank 0's frame (CUDA IPC over NVLink)
+                handle = [r.frame_export() if rank == 0 else None]
+                dist.broadcast_object_list(handle, src=0)
+                r.frame_attach(handle[0])
         renderers.append((label, sc, r))
 
     frame_bytes = max(sc.px_width * sc.px_height * 4 for _, sc in scenes)
     host_frame = torch.empty(frame_bytes, dtype=torch.uint8).pin_memory()
     host_cam = torch.from_numpy(m.copy()).pin_memory()
 
-    def step_device():
-        for _, _, r in renderers:
-            r.update(m)
-
     def step_e2e():
+        """The user-facing call with HOST buffers: camera matrix in, finished frame in pinned host memory out."""
         for _, sc, r in renderers:
-            r.update(host_cam.numpy())                                  # H2D: the camera matrix (kernel params)
-            r.gather_into(host_frame.data_ptr(), sc.px_width * sc.px_height * 4)   # D2H: the finished frame
+            nbytes = sc.px_width * sc.px_height * 4
+            if world == 1:
+                r.update_to_host(host_cam.numpy(), host_frame.data_ptr(), nbytes)
+            else:
+                r.update(host_cam.numpy())
+                if rank == 0:           # the frame is assembled on GPU 0 (north_star); rank 0 hands it to the host
+                    r.gather_into(host_frame.data_ptr(), nbytes)
+
+    # ---- census (untimed): rays and tests of one step, with the kernel's counters on -----------------
+    local_counts = {}
+    for label, _, r in renderers:
+        r.set_option("count", 1)
+        r.update(m)
+        local_counts[label] = r.counters()
+        r.set_option("count", 0)        # counters are instrumentation, not part of the frame: off while timing
 
     # ---- device-resident timing ------------------------------------------------------------------
     for _ in range(max(args.warmup, 3)):
-        step_device()
+        for _, _, r in renderers:
+            r.update(m)
     sampler = ClockSampler(local)
     per_scene = {label: {"render_ms": 0.0, "gather_ms": 0.0} for label, _, _ in renderers}
-    barrier()
+    launches = 0
     if rank == 0:
-        sampler.start()
+        sampler.start()                 # before the barrier: forking nvidia-smi must not delay rank 0's first frame
+        time.sleep(0.05)
+    barrier()
     t0 = time.perf_counter()
+    ev_ms = 0.0
     for _ in range(args.steps):
         for label, _, r in renderers:
-            r.update(m)
+            ev_ms += r.update(m)        # CUDA events on the library's render stream: first launch -> frame complete
             t = r.timing()
             per_scene[label]["render_ms"] += t["render_ms"]
             per_scene[label]["gather_ms"] += t["gather_ms"]
+            launches += r.launches()
     barrier()
     dt = time.perf_counter() - t0
     clocks = sampler.stop() if rank == 0 else None
@@ -269,21 +289,20 @@ def run_b200(args):
     barrier()
     dt_e2e = time.perf_counter() - t0
 
-    # ---- census: rays and canonical flops of one step, summed over ranks ----------------------------
-    local_counts = {}
-    for label, _, r in renderers:
-        local_counts[label] = r.counters()
     keys = list(binding.COUNTER_FIELDS)
     mat = torch.tensor([[local_counts[label][k] for k in keys] for label, _, _ in renderers], dtype=torch.int64,
                        device="cuda")
-    times = torch.tensor([dt, dt_e2e], dtype=torch.float64, device="cuda")
+    times = torch.tensor([dt, dt_e2e, ev_ms / 1e3], dtype=torch.float64, device="cuda")
     kern = torch.tensor([[per_scene[label]["render_ms"], per_scene[label]["gather_ms"]] for label, _, _ in renderers],
                         dtype=torch.float64, device="cuda")
+    nl = torch.tensor([launches], dtype=torch.int64, device="cuda")
     if world > 1:
         dist.all_reduce(mat, op=dist.ReduceOp.SUM)
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
         dist.all_reduce(kern, op=dist.ReduceOp.MAX)
+        dist.all_reduce(nl, op=dist.ReduceOp.SUM)
     mat, times, kern = mat.cpu().numpy(), times.cpu().numpy(), kern.cpu().numpy() / args.steps
+    launches = int(nl.item())
 
     if rank == 0:
         peaks = load_peaks()
@@ -293,7 +312,8 @@ def run_b200(args):
         totals = {k: int(mat[:, i].sum()) for i, k in enumerate(keys)}
         rays_step = totals["primary_rays"] + totals["reflection_rays"] + totals["shadow_rays"]
         flops_step = canonical_flops(totals)
-        ms_step = times[0] / args.steps * 1e3
+        ms_step = times[2] / args.steps * 1e3          # CUDA events, max over ranks
+        ms_wall = times[0] / args.steps * 1e3          # host clock around the same loop (barrier + sync on both sides)
         ms_e2e = times[1] / args.steps * 1e3
         render_ms_sum = float(kern[:, 0].sum())          # per step, max over ranks per scene
         scenes_out = {}
@@ -308,18 +328,26 @@ def run_b200(args):
                 "fb_write_gbs": sc.px_width * sc.px_height * 4 / rms / 1e6,
             }
         achieved = flops_step / render_ms_sum / 1e9 / world    # TFLOP/s per GPU over the render kernels
-        launches = args.steps * len(renderers) * (1 + (1 if world > 1 else 0))
+        # the same flops split by the pipe that executes them here: sphere tests run through the FP32 filter, every
+        # other class (and hit / shading geometry) is FP64 in the reference's operation order, at half the FP32 rate
+        fl32 = float(totals["tests_sphere"] * FLOPS["tests_sphere"] + totals["lit"] * FLOPS["lit"])
+        fl64 = flops_step - fl32
+        t_min_ms = (fl32 / fp32_peak + fl64 / (fp32_peak / 2.0)) / 1e9 / world
         line = {
             "metric": METRIC, "value": rays_step / ms_step / 1e3, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "ms_per_step_wall": ms_wall, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": args.workload, "description": desc, "frames_per_step": len(renderers),
                        "rays_per_step": rays_step, "kernel": args.kernel,
-                       "parallelism": "strips{}x{}rows".format(world, args.strip_rows) if world > 1 else "1gpu",
+                       "parallelism": "strips{}x{}rows,{}".format(world, args.strip_rows, "p2p-store+barrier" if fused else
+                                                                  "nccl-allgather") if world > 1 else "1gpu",
+                       "timing": "CUDA events on the render stream per frame, summed; max over ranks",
                        "l2": "outputs ({} MB per step) exceed the 126 MB L2; the scene (KBs) is cache-resident by design"
                              .format(len(renderers) * frame_bytes // 1000000)},
             "e2e": {"value": rays_step / ms_e2e / 1e3, "unit": UNIT, "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": len(renderers) * 128,
+                    "how": "rt_b200_update_to_host: banded render with the D2H copy of finished bands overlapped"
+                           if world == 1 else "rt_b200_update on every rank + rt_b200_gather to pinned host memory on rank 0",
                     "d2h_bytes_per_step": int(sum(sc.px_width * sc.px_height * 4 for _, sc, _ in renderers))},
             "gpu_launches": launches,
             "clocks": clocks,
@@ -327,6 +355,8 @@ def run_b200(args):
                          "frac": achieved / fp32_peak, "traffic": None,
                          "peak_source": "148 SMs x 128 lanes x 2 x sm_max_mhz of MEASURED_PEAKS.json ({})".format(peaks["_source"]),
                          "algorithmic_gflop_per_step": flops_step / 1e9, "kernel_ms_per_step": render_ms_sum,
+                         "blended": {"frac": t_min_ms / render_ms_sum, "fp32_gflop": fl32 / 1e9, "fp64_gflop": fl64 / 1e9,
+                                     "what": "time at peak (fp32 flops / FP32 peak + fp64 flops / (FP32 peak / 2)) / kernel time"},
                          "note": "canonical flops of SURVEY.md §8d over the render kernels' CUDA-event time; "
                                  "the path is compute-bound (not hbm/tensor)",
                          "hbm": {"achieved": len(renderers) * frame_bytes / render_ms_sum / 1e6, "peak": peaks["hbm_gbs"],
@@ -351,7 +381,7 @@ def cpu_baseline(pkg, scenes, args) -> dict:
     cores = os.cpu_count() or 1
     kind = "reference" if oracle_py.have_ref() else "port"
     m = camera.TEST_POSES["initial"]
-    ystep = args.ref_row_step
+    ystep = args.ref_row_step or 1
     rays, secs = 0, 0.0
     for _, sc in scenes:
         _, _, cnt = oracle_py.PortOracle(sc).render_rows(m, 0, sc.px_height, ystep, threads=cores, count=True)
@@ -374,7 +404,9 @@ def main():
     ap.add_argument("--workload", default="bundled4k", choices=["bundled4k", "synthetic"])
     ap.add_argument("--kernel", type=int, default=1)
     ap.add_argument("--strip-rows", type=int, default=8)
-    ap.add_argument("--ref-row-step", type=int, default=8)
+    ap.add_argument("--ref-row-step", type=int, default=0, help="CPU legs render every n-th image row (0 = 1 for the "
+                    "cpu_baseline leg, 2 for --impl reference steps)")
+    ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"], help="multi-GPU frame assembly")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -26,9 +26,11 @@ COUNTER_FIELDS = ("primary_rays", "reflection_rays", "shadow_rays", "hits", "lit
 # every symbol include/rt_b200.h declares
 EXPORTS = ("rt_b200_upload_scene", "rt_b200_update", "rt_b200_gather", "rt_b200_destroy", "rt_b200_last_error",
            "rt_b200_comm_unique_id", "rt_b200_comm_init", "rt_b200_get_counters", "rt_b200_set_option",
-           "rt_b200_get_timing", "rt_b200_get_class_counts", "rt_b200_strip_layout", "rt_b200_version")
+           "rt_b200_get_timing", "rt_b200_get_class_counts", "rt_b200_strip_layout", "rt_b200_version",
+           "rt_b200_update_to_host", "rt_b200_frame_export", "rt_b200_frame_attach", "rt_b200_get_launches")
 
 UNIQUE_ID_BYTES = 128
+IPC_HANDLE_BYTES = 64
 
 
 class RtError(RuntimeError):
@@ -64,6 +66,10 @@ def load_library():
     L.rt_b200_get_timing.argtypes = [vp, C.POINTER(C.c_float * 2)]
     L.rt_b200_get_class_counts.argtypes = [vp, C.POINTER(C.c_uint32 * 4)]
     L.rt_b200_version.restype = C.c_char_p
+    L.rt_b200_update_to_host.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(C.c_float)]
+    L.rt_b200_frame_export.argtypes = [vp, vp]
+    L.rt_b200_frame_attach.argtypes = [vp, vp]
+    L.rt_b200_get_launches.argtypes = [vp, C.POINTER(C.c_uint32)]
     L.rt_b200_strip_layout.argtypes = [C.c_uint32, C.c_uint32, C.c_int, C.c_int, vp, C.c_size_t, C.POINTER(C.c_uint32)]
     _lib = L
     return L
@@ -115,6 +121,29 @@ class Renderer:
         ms = C.c_float()
         _check(load_library().rt_b200_update(self._h, _dp(m), C.byref(ms)))
         return ms.value
+
+    def update_to_host(self, camera_matrix, host_ptr: int, nbytes: int) -> float:
+        """update() + result sink in one call: the frame lands in caller-owned (ideally pinned) host memory, the
+        device->host copy of finished row bands overlapping the rendering of the next ones."""
+        m = np.ascontiguousarray(camera_matrix, dtype=np.float64).reshape(16)
+        ms = C.c_float()
+        _check(load_library().rt_b200_update_to_host(self._h, _dp(m), C.c_void_p(host_ptr), nbytes, C.byref(ms)))
+        return ms.value
+
+    def frame_export(self) -> bytes:
+        """Rank 0: IPC handle of the assembled frame every rank's kernel will write into (fused gather)."""
+        buf = (C.c_char * IPC_HANDLE_BYTES)()
+        _check(load_library().rt_b200_frame_export(self._h, buf))
+        return bytes(buf)
+
+    def frame_attach(self, handle: bytes):
+        buf = C.create_string_buffer(handle, IPC_HANDLE_BYTES)
+        _check(load_library().rt_b200_frame_attach(self._h, buf))
+
+    def launches(self) -> int:
+        n = C.c_uint32()
+        _check(load_library().rt_b200_get_launches(self._h, C.byref(n)))
+        return int(n.value)
 
     def gather(self, out: np.ndarray | None = None) -> np.ndarray:
         """Frame as uint8 [H, W, 4], row 0 = bottom of the picture."""

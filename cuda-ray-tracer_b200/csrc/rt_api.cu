@@ -14,6 +14,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <algorithm>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -50,6 +51,7 @@ struct NcclApi {
     ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
     const char *(*GetErrorString)(ncclResult_t) = nullptr;
 };
 NcclApi g_nccl;
@@ -65,7 +67,8 @@ int load_nccl()
     g_nccl.CommDestroy = (decltype(g_nccl.CommDestroy)) dlsym(h, "ncclCommDestroy");
     g_nccl.AllGather = (decltype(g_nccl.AllGather)) dlsym(h, "ncclAllGather");
     g_nccl.GetErrorString = (decltype(g_nccl.GetErrorString)) dlsym(h, "ncclGetErrorString");
-    if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.CommDestroy || !g_nccl.AllGather ||
+    g_nccl.AllReduce = (decltype(g_nccl.AllReduce)) dlsym(h, "ncclAllReduce");
+    if (!g_nccl.AllReduce || !g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.CommDestroy || !g_nccl.AllGather ||
         !g_nccl.GetErrorString) {
         dlclose(h);
         return fail(RT_B200_ERR_NCCL, "libnccl.so.2 lacks a required symbol");
@@ -92,6 +95,8 @@ cudaError_t upload(const std::vector<T> &host, T **dev)
 }
 
 } // namespace
+
+#define RT_MAX_BANDS 16
 
 struct rt_b200_ctx {
     int device = 0, rank = 0, world = 1;
@@ -127,11 +132,23 @@ struct rt_b200_ctx {
     bool buffers_dirty = true;
 
     int kernel_kind = 1;
+    int launches = 0;                // render launches of the last update
     bool count = true;
     bool rendered = false;
 
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev_start = nullptr, ev_render = nullptr, ev_end = nullptr;
+    // fused gather (world > 1): the assembled frame lives on rank 0, double-buffered; the other ranks map it through
+    // CUDA IPC and their render kernels store pixels straight into it over NVLink
+    uchar4 *d_shared_base = nullptr;   // rank 0: cudaMalloc; other ranks: cudaIpcOpenMemHandle
+    uchar4 *d_shared[2] = {nullptr, nullptr};
+    bool shared_owner = false, shared_ready = false;
+    int parity = 0;
+    int *d_barrier = nullptr;
+    const uchar4 *last_frame = nullptr;   // what rt_b200_gather hands out
+
+    cudaStream_t stream = nullptr, copy_stream = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_render = nullptr, ev_end = nullptr, ev_copy = nullptr;
+    cudaEvent_t ev_band[RT_MAX_BANDS] = {};
+    int host_bands = 0;                   // 0 = automatic
     float ms_render = 0, ms_gather = 0;
 
     ncclComm_t comm = nullptr;
@@ -335,6 +352,10 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     up(cudaEventCreate(&c->ev_start), "event");
     up(cudaEventCreate(&c->ev_render), "event");
     up(cudaEventCreate(&c->ev_end), "event");
+    up(cudaEventCreate(&c->ev_copy), "event");
+    up(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking), "copy stream");
+    for (int b = 0; b < RT_MAX_BANDS; b++) up(cudaEventCreateWithFlags(&c->ev_band[b], cudaEventDisableTiming), "event");
+    up(cudaMalloc((void **) &c->d_barrier, sizeof(int)), "barrier word");
     if (rc != RT_B200_OK) {
         rt_b200_destroy(c);
         return rc;
@@ -379,12 +400,45 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     return RT_B200_OK;
 }
 
-int rt_b200_update(rt_b200_ctx *c, const double camera_matrix[16], float *elapsed_ms)
+} // extern "C"
+
+namespace {
+
+// One render launch of the selected kernel over the packed rows [f.row0, f.row0 + f.rows).
+int launch_kernel(rt_b200_ctx *c, const rt::FrameParams &f)
+{
+    if (c->kernel_kind == 0) {
+        CUDA_TRY(rt::launch_render_exact(c->view, f, c->stream));
+    }
+    else if (c->kernel_kind == 2 && c->qscene) {
+        rt::QueueLaunch ql{};
+        ql.tile_counter = c->d_tile_counter;
+        ql.tables = c->qtables;
+        ql.scene = c->qscene;
+        ql.primary_safe = (fabs(f.origin[0]) < 1e9 && fabs(f.origin[1]) < 1e9 && fabs(f.origin[2]) < 1e9) ? 1 : 0;
+        ql.shadow_cache = c->shadow_cache;
+        ql.variant = c->queue_variant;
+        CUDA_TRY(rt::launch_render_queue(c->view, f, ql, c->stream));
+    }
+    else {   // kernel 1, and kernel 2 for scenes that exceed the queue kernel's parameter block
+        rt::WaveLaunch wl{c->d_tile_counter, c->d_cubic_mask, c->sphere_r2_max, c->shadow_cache, c->wave_variant};
+        CUDA_TRY(rt::launch_render_wave(c->view, f, wl, c->stream));
+    }
+    return RT_B200_OK;
+}
+
+// update() proper.  host_sink != nullptr (single GPU): the frame is rendered in row bands and every finished band is
+// copied to the host on a second stream while the next band renders, so the device->host transfer of the frame
+// overlaps the rendering instead of following it.
+int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink, size_t host_bytes, float *elapsed_ms)
 {
     if (!c || !camera_matrix) return fail(RT_B200_ERR_ARG, "null argument");
     CUDA_TRY(cudaSetDevice(c->device));
     int rc = ensure_buffers(c);
     if (rc != RT_B200_OK) return rc;
+    const size_t frame_bytes = sizeof(uchar4) * (size_t) c->width * c->height;
+    if (host_sink && host_bytes < frame_bytes)
+        return fail(RT_B200_ERR_ARG, "host buffer holds %zu bytes, frame needs %zu", host_bytes, frame_bytes);
 
     rt::FrameParams f;
     std::memcpy(f.m, camera_matrix, sizeof(f.m));
@@ -401,45 +455,142 @@ int rt_b200_update(rt_b200_ctx *c, const double camera_matrix[16], float *elapse
     f.rank = c->rank;
     f.world = c->world;
     f.local_rows = c->local_rows;
-    f.out = c->d_local;
+    f.row0 = 0;
+    f.rows = c->local_rows;
     f.counters = c->count ? c->d_counters : nullptr;
+    const bool shared = c->world > 1 && c->comm && c->shared_ready;
+    if (shared) {
+        c->parity ^= 1;                 // rank 0 may still be reading the previous frame: write the other buffer
+        f.out = c->d_shared[c->parity];
+        f.direct = 1;
+    }
+    else {
+        f.out = c->d_local;
+        f.direct = 0;
+    }
+
+    // row bands of the streamed host copy (single GPU only): ~4 MB each, whole 16-row tiles
+    int n_bands = 1;
+    const bool streamed = host_sink != nullptr && c->world == 1;
+    if (streamed) {
+        n_bands = c->host_bands > 0 ? c->host_bands : (int) (frame_bytes / (4u << 20));
+        if (n_bands > RT_MAX_BANDS) n_bands = RT_MAX_BANDS;
+        if (n_bands > (c->local_rows + 15) / 16) n_bands = (c->local_rows + 15) / 16;
+        if (n_bands < 1) n_bands = 1;
+    }
+    const int band_rows = ((c->local_rows + n_bands - 1) / n_bands + 15) & ~15;
 
     if (c->count) CUDA_TRY(cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long) * rt::CNT_COUNT, c->stream));
     CUDA_TRY(cudaEventRecord(c->ev_start, c->stream));
-    if (c->kernel_kind == 0) {
-        CUDA_TRY(rt::launch_render_exact(c->view, f, c->stream));
-    }
-    else if (c->kernel_kind == 2 && c->qscene) {
-        // the primary-ray table depends on the camera origin: one small setup launch per frame
+    if (c->kernel_kind == 2 && c->qscene)   // the primary-ray table depends on the camera origin: one setup launch per frame
         CUDA_TRY(rt::build_queue_tables(c->view, c->qtables, *c->qscene, 1, 2, f.origin, c->stream));
-        rt::QueueLaunch ql{};
-        ql.tile_counter = c->d_tile_counter;
-        ql.tables = c->qtables;
-        ql.scene = c->qscene;
-        ql.primary_safe = (fabs(f.origin[0]) < 1e9 && fabs(f.origin[1]) < 1e9 && fabs(f.origin[2]) < 1e9) ? 1 : 0;
-        ql.shadow_cache = c->shadow_cache;
-        ql.variant = c->queue_variant;
-        ql.direct = 0;
-        CUDA_TRY(rt::launch_render_queue(c->view, f, ql, c->stream));
-    }
-    else {
-        rt::WaveLaunch wl{c->d_tile_counter, c->d_cubic_mask, c->sphere_r2_max, c->shadow_cache, c->wave_variant};
-        CUDA_TRY(rt::launch_render_wave(c->view, f, wl, c->stream));
+    c->launches = 0;
+    for (int b = 0; b < n_bands; b++) {
+        f.row0 = b * band_rows;
+        f.rows = std::min(band_rows, c->local_rows - f.row0);
+        if (f.rows <= 0) break;
+        rc = launch_kernel(c, f);
+        if (rc != RT_B200_OK) return rc;
+        c->launches++;
+        if (streamed) {
+            CUDA_TRY(cudaEventRecord(c->ev_band[b], c->stream));
+            CUDA_TRY(cudaStreamWaitEvent(c->copy_stream, c->ev_band[b], 0));
+            const size_t off = (size_t) f.row0 * c->width;
+            CUDA_TRY(cudaMemcpyAsync(static_cast<uchar4 *>(host_sink) + off, c->d_local + off,
+                                     sizeof(uchar4) * (size_t) f.rows * c->width, cudaMemcpyDeviceToHost, c->copy_stream));
+        }
     }
     CUDA_TRY(cudaEventRecord(c->ev_render, c->stream));
+    c->last_frame = c->d_local;
     if (c->world > 1 && c->comm) {
-        const size_t bytes = sizeof(uchar4) * (size_t) c->width * c->local_rows;
-        NCCL_TRY(g_nccl.AllGather(c->d_local, c->d_gathered, bytes, ncclUint8, c->comm, c->stream));
-        CUDA_TRY(rt::launch_unpack_strips(c->d_gathered, c->d_frame, c->width, c->height, c->strip_rows, c->world,
-                                          c->local_rows, c->stream));
+        if (shared) {
+            // every rank's pixels are already in rank 0's frame; the 4-byte all-reduce is the frame-complete barrier
+            NCCL_TRY(g_nccl.AllReduce(c->d_barrier, c->d_barrier, 1, ncclInt, ncclSum, c->comm, c->stream));
+            c->last_frame = c->d_shared[c->parity];
+        }
+        else {
+            const size_t bytes = sizeof(uchar4) * (size_t) c->width * c->local_rows;
+            NCCL_TRY(g_nccl.AllGather(c->d_local, c->d_gathered, bytes, ncclUint8, c->comm, c->stream));
+            CUDA_TRY(rt::launch_unpack_strips(c->d_gathered, c->d_frame, c->width, c->height, c->strip_rows, c->world,
+                                              c->local_rows, c->stream));
+            c->last_frame = c->d_frame;
+        }
+    }
+    else if (c->world > 1) {
+        c->last_frame = nullptr;   // assembled on demand by rt_b200_gather (this rank's rows only)
     }
     CUDA_TRY(cudaEventRecord(c->ev_end, c->stream));
+    if (streamed) {
+        CUDA_TRY(cudaEventRecord(c->ev_copy, c->copy_stream));
+        CUDA_TRY(cudaStreamWaitEvent(c->stream, c->ev_copy, 0));   // keep the next frame from overwriting rows in flight
+        CUDA_TRY(cudaEventRecord(c->ev_copy, c->stream));
+        CUDA_TRY(cudaEventSynchronize(c->ev_copy));
+    }
     CUDA_TRY(cudaEventSynchronize(c->ev_end));
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaEventElapsedTime(&c->ms_render, c->ev_start, c->ev_render));
     CUDA_TRY(cudaEventElapsedTime(&c->ms_gather, c->ev_render, c->ev_end));
+    float total = c->ms_render + c->ms_gather;
+    if (streamed) CUDA_TRY(cudaEventElapsedTime(&total, c->ev_start, c->ev_copy));
     c->rendered = true;
-    if (elapsed_ms) *elapsed_ms = c->ms_render + c->ms_gather;
+    if (elapsed_ms) *elapsed_ms = total;
+    if (host_sink && !streamed) return rt_b200_gather(c, host_sink, host_bytes, nullptr);
+    return RT_B200_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int rt_b200_update(rt_b200_ctx *c, const double camera_matrix[16], float *elapsed_ms)
+{
+    return render_frame(c, camera_matrix, nullptr, 0, elapsed_ms);
+}
+
+int rt_b200_update_to_host(rt_b200_ctx *c, const double camera_matrix[16], void *host_rgba8, size_t host_bytes,
+                           float *elapsed_ms)
+{
+    if (!host_rgba8) return fail(RT_B200_ERR_ARG, "host buffer is null");
+    return render_frame(c, camera_matrix, host_rgba8, host_bytes, elapsed_ms);
+}
+
+int rt_b200_frame_export(rt_b200_ctx *c, void *handle_out)
+{
+    if (!c || !handle_out) return fail(RT_B200_ERR_ARG, "null argument");
+    if (c->world < 2) return fail(RT_B200_ERR_ARG, "a shared frame needs world_size > 1");
+    CUDA_TRY(cudaSetDevice(c->device));
+    static_assert(sizeof(cudaIpcMemHandle_t) == RT_B200_IPC_HANDLE_BYTES, "cudaIpcMemHandle_t size");
+    const size_t px = (size_t) c->width * c->height;
+    if (!c->d_shared_base) {
+        CUDA_TRY(cudaMalloc((void **) &c->d_shared_base, 2 * sizeof(uchar4) * px));
+        CUDA_TRY(cudaMemset(c->d_shared_base, 0, 2 * sizeof(uchar4) * px));
+        c->shared_owner = true;
+    }
+    if (!c->shared_owner) return fail(RT_B200_ERR_STATE, "this context maps another rank's frame");
+    cudaIpcMemHandle_t h;
+    CUDA_TRY(cudaIpcGetMemHandle(&h, c->d_shared_base));
+    std::memcpy(handle_out, &h, sizeof(h));
+    return RT_B200_OK;
+}
+
+int rt_b200_frame_attach(rt_b200_ctx *c, const void *handle)
+{
+    if (!c || !handle) return fail(RT_B200_ERR_ARG, "null argument");
+    if (c->world < 2) return fail(RT_B200_ERR_ARG, "a shared frame needs world_size > 1");
+    CUDA_TRY(cudaSetDevice(c->device));
+    const size_t px = (size_t) c->width * c->height;
+    if (!c->shared_owner) {
+        if (c->d_shared_base) return fail(RT_B200_ERR_STATE, "a shared frame is already attached");
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, handle, sizeof(h));
+        void *base = nullptr;
+        CUDA_TRY(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+        c->d_shared_base = static_cast<uchar4 *>(base);
+    }
+    c->d_shared[0] = c->d_shared_base;
+    c->d_shared[1] = c->d_shared_base + px;
+    c->shared_ready = true;
+    CUDA_TRY(cudaMemset(c->d_barrier, 0, sizeof(int)));
     return RT_B200_OK;
 }
 
@@ -449,20 +600,16 @@ int rt_b200_gather(rt_b200_ctx *c, void *host_rgba8, size_t host_bytes, const vo
     if (!c->rendered) return fail(RT_B200_ERR_STATE, "rt_b200_gather before the first rt_b200_update");
     CUDA_TRY(cudaSetDevice(c->device));
     const size_t frame_bytes = sizeof(uchar4) * (size_t) c->width * c->height;
-    const uchar4 *frame = c->d_local;
-    if (c->world > 1) {
+    const uchar4 *frame = c->last_frame;
+    if (!frame) {
+        // world > 1 without a communicator: expose this rank's rows in place, the others stay zero
+        CUDA_TRY(cudaMemsetAsync(c->d_gathered, 0, sizeof(uchar4) * (size_t) c->width * c->local_rows * c->world, c->stream));
+        CUDA_TRY(cudaMemcpyAsync(c->d_gathered + (size_t) c->rank * c->local_rows * c->width, c->d_local,
+                                 sizeof(uchar4) * (size_t) c->width * c->local_rows, cudaMemcpyDeviceToDevice, c->stream));
+        CUDA_TRY(rt::launch_unpack_strips(c->d_gathered, c->d_frame, c->width, c->height, c->strip_rows, c->world,
+                                          c->local_rows, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
         frame = c->d_frame;
-        if (!c->comm) {
-            // no communicator: expose this rank's rows in place, the others stay zero
-            CUDA_TRY(cudaMemsetAsync(c->d_gathered, 0, sizeof(uchar4) * (size_t) c->width * c->local_rows * c->world,
-                                     c->stream));
-            CUDA_TRY(cudaMemcpyAsync(c->d_gathered + (size_t) c->rank * c->local_rows * c->width, c->d_local,
-                                     sizeof(uchar4) * (size_t) c->width * c->local_rows, cudaMemcpyDeviceToDevice,
-                                     c->stream));
-            CUDA_TRY(rt::launch_unpack_strips(c->d_gathered, c->d_frame, c->width, c->height, c->strip_rows, c->world,
-                                              c->local_rows, c->stream));
-            CUDA_TRY(cudaStreamSynchronize(c->stream));
-        }
     }
     if (host_rgba8) {
         if (host_bytes < frame_bytes)
@@ -498,6 +645,15 @@ int rt_b200_destroy(rt_b200_ctx *c)
     if (c->ev_start) cudaEventDestroy(c->ev_start);
     if (c->ev_render) cudaEventDestroy(c->ev_render);
     if (c->ev_end) cudaEventDestroy(c->ev_end);
+    if (c->ev_copy) cudaEventDestroy(c->ev_copy);
+    for (int b = 0; b < RT_MAX_BANDS; b++)
+        if (c->ev_band[b]) cudaEventDestroy(c->ev_band[b]);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    cudaFree(c->d_barrier);
+    if (c->d_shared_base) {
+        if (c->shared_owner) cudaFree(c->d_shared_base);
+        else cudaIpcCloseMemHandle(c->d_shared_base);
+    }
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
     return RT_B200_OK;
@@ -563,6 +719,10 @@ int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
         if (value < -1 || value > 1) return fail(RT_B200_ERR_ARG, "shadow_cache must be -1, 0 or 1");
         c->shadow_cache = (int) value;
     }
+    else if (!std::strcmp(name, "host_bands")) {
+        if (value < 0 || value > RT_MAX_BANDS) return fail(RT_B200_ERR_ARG, "host_bands must be 0..%d", RT_MAX_BANDS);
+        c->host_bands = (int) value;
+    }
     else if (!std::strcmp(name, "count")) {
         c->count = value != 0;
     }
@@ -595,6 +755,16 @@ int rt_b200_get_timing(rt_b200_ctx *c, float out_ms[2])
     if (!c || !out_ms) return fail(RT_B200_ERR_ARG, "null argument");
     out_ms[0] = c->ms_render;
     out_ms[1] = c->ms_gather;
+    return RT_B200_OK;
+}
+
+int rt_b200_get_launches(rt_b200_ctx *c, uint32_t *launches)
+{
+    if (!c || !launches) return fail(RT_B200_ERR_ARG, "null argument");
+    uint32_t n = (uint32_t) c->launches;
+    if (c->kernel_kind == 2 && c->qscene && c->view.n_sphere > 0) n += 1;   // primary-ray table
+    if (c->world > 1 && c->comm && !c->shared_ready) n += 1;                 // strip un-interleave
+    *launches = n;
     return RT_B200_OK;
 }
 

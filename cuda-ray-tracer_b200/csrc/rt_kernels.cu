@@ -20,9 +20,10 @@ render_exact_kernel(const __grid_constant__ SceneView sc, const __grid_constant_
 {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int x = blockIdx.x * TILE_W + (warp & 3) * 8 + (lane & 7);
-    const int lrow = blockIdx.y * TILE_H + (warp >> 2) * 4 + (lane >> 3);
+    const int lrow = f.row0 + blockIdx.y * TILE_H + (warp >> 2) * 4 + (lane >> 3);
     const int y = local_to_image_row(lrow, f.strip_rows, f.rank, f.world);
-    const bool live = x < f.width && lrow < f.local_rows && y < f.height;
+    const bool in_band = x < f.width && lrow < f.row0 + f.rows && lrow < f.local_rows;
+    const bool live = in_band && y < f.height;
 
     Tally tl;
     tl.clear();
@@ -67,9 +68,9 @@ render_exact_kernel(const __grid_constant__ SceneView sc, const __grid_constant_
                 if (stop) break;
             }
         }
-        f.out[(size_t) lrow * f.width + x] = pack_rgba8(out.x, out.y, out.z);
+        f.out[out_index(f, lrow, y, x)] = pack_rgba8(out.x, out.y, out.z);
     }
-    else if (x < f.width && lrow < f.local_rows) {
+    else if (in_band && !f.direct) {
         f.out[(size_t) lrow * f.width + x] = make_uchar4(0, 0, 0, 0);   // padding row past the image
     }
     flush_tally(tl, f.counters);
@@ -78,7 +79,7 @@ render_exact_kernel(const __grid_constant__ SceneView sc, const __grid_constant_
 cudaError_t launch_render_exact(const SceneView &scene, const FrameParams &frame, cudaStream_t stream)
 {
     dim3 block(TILE_W * TILE_H);
-    dim3 grid((frame.width + TILE_W - 1) / TILE_W, (frame.local_rows + TILE_H - 1) / TILE_H);
+    dim3 grid((frame.width + TILE_W - 1) / TILE_W, (frame.rows + TILE_H - 1) / TILE_H);
     render_exact_kernel<<<grid, block, 0, stream>>>(scene, frame);
     return cudaGetLastError();
 }

@@ -37,7 +37,6 @@ struct QueueLaunch {
     int shadow_cache;                   // 1 / 0 / -1 = automatic
     int variant;                        // 0 = automatic; 1: 256 threads, tables resident; 2: 512 threads, streamed;
                                         // 3: 512 threads, resident; 4: 256 threads, streamed
-    int direct;                         // pixels go to their image position (frame shared across GPUs)
 };
 // True when planes / quadrics / cubics / lights fit the kernel-parameter block; otherwise use the wavefront kernel.
 bool queue_scene_fits(const SceneView &scene);

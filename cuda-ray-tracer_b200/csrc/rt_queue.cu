@@ -208,12 +208,12 @@ render_queue_kernel(const __grid_constant__ SceneView g, const __grid_constant__
             const int tile = S.tile;
             const int tx = tile % cfg.tiles_x, ty = tile / cfg.tiles_x;
             const int x = tx * 32 + (warp & 3) * 8 + (lane & 7);
-            const int lrow = ty * TILE_ROWS + (warp >> 2) * 4 + (lane >> 3);
+            const int lrow = f.row0 + ty * TILE_ROWS + (warp >> 2) * 4 + (lane >> 3);
             const int y = local_to_image_row(lrow, f.strip_rows, f.rank, f.world);
-            const bool in_buf = x < f.width && lrow < f.local_rows;
+            const bool in_buf = x < f.width && lrow < f.row0 + f.rows && lrow < f.local_rows;
             active = in_buf && y < f.height;
-            pixel = cfg.direct ? y * f.width + x : lrow * f.width + x;
-            if (in_buf && !active && !cfg.direct) f.out[pixel] = make_uchar4(0, 0, 0, 0);   // padding row past the image
+            pixel = (int) out_index(f, lrow, y, x);
+            if (in_buf && !active && !f.direct) f.out[pixel] = make_uchar4(0, 0, 0, 0);   // padding row past the image
             if (active) {
                 qo = cam_origin;
                 qd = primary_dir(f, cam_origin, x, y);
@@ -543,7 +543,7 @@ cudaError_t launch_queue_variant(const SceneView &scene, const FrameParams &fram
         attr_set = true;
     }
     cfg.tiles_x = (frame.width + 31) / 32;
-    cfg.tiles_y = (frame.local_rows + W / 32 - 1) / (W / 32);
+    cfg.tiles_y = (frame.rows + W / 32 - 1) / (W / 32);
     int per_sm = 1;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W, smem);
     if (e != cudaSuccess) return e;
@@ -634,7 +634,6 @@ cudaError_t launch_render_queue(const SceneView &scene, const FrameParams &frame
     cfg.use_shadow_cache = ql.shadow_cache >= 0 ? ql.shadow_cache : (scene.n_objects >= 4 ? 1 : 0);
     // rough issue-slot cost of one full pass over each stage: cheaper stage first when no occluder is cached
     cfg.poly_first = (15LL * scene.n_plane + 150LL * scene.n_quadric + 700LL * scene.n_cubic < 7LL * scene.n_sphere) ? 1 : 0;
-    cfg.direct = ql.direct;
     cfg.r_max = ql.tables.r_max;
     cfg.center_max = scene.sphere_center_max;
     cfg.center_norm_max = ql.tables.center_norm_max;

@@ -38,7 +38,6 @@ struct QueueConfig {
     int tables_safe, primary_safe;     // magnitudes small enough for the FP32 tables (else every sphere is tested exactly)
     int use_shadow_cache;
     int poly_first;                    // any-hit rays without a cached occluder: planes/quadrics/cubics before spheres
-    int direct;                        // 1: pixels are written at their image position (frame shared across GPUs)
     float r_max, center_max, center_norm_max, r2_max;
     const float4 *tables;              // global: [2 + n_lights][n_sphere_pad]  (0 generic, 1 primary, 2+j light j)
 };

@@ -64,7 +64,11 @@ struct FrameParams {
     // multi-GPU interleave: this rank renders strips s with s % world == rank, packed contiguously
     int strip_rows, rank, world;
     int local_rows;        // rows in this rank's packed buffer (including padding rows past the image)
-    uchar4 *out;           // [local_rows][width]
+    int row0, rows;        // this launch renders the packed rows [row0, row0 + rows) (a band; whole frame: 0, local_rows)
+    int direct;            // 0: out is this rank's packed buffer [local_rows][width]
+                           // 1: out is the assembled frame [height][width] (possibly in a peer GPU's memory): pixels
+                           //    are stored at their image position and padding rows are not written
+    uchar4 *out;
     unsigned long long *counters;  // [CNT_COUNT] or nullptr
 };
 
@@ -74,6 +78,12 @@ __host__ __device__ inline int local_to_image_row(int local_row, int strip_rows,
     int s_local = local_row / strip_rows;
     int r = local_row - s_local * strip_rows;
     return (s_local * world + rank) * strip_rows + r;
+}
+
+// index into FrameParams::out of pixel x of packed row lrow (image row y)
+__host__ __device__ inline size_t out_index(const FrameParams &f, int lrow, int y, int x)
+{
+    return (size_t) (f.direct ? y : lrow) * f.width + x;
 }
 
 __host__ __device__ inline size_t align16(size_t v) { return (v + 15) & ~(size_t) 15; }

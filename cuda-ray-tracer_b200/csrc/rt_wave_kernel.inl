@@ -84,7 +84,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
     tl.clear();
     const d3 cam_origin = d3{f.origin[0], f.origin[1], f.origin[2]};
     const int n_tiles = cfg.tiles_x * cfg.tiles_y;
-    const bool vec_ok = (f.width & 3) == 0;
+    const bool vec_ok = (f.width & 3) == 0;   // rows start 16-byte aligned (packed and assembled layout alike)
     bool tiles_left = true;
     unsigned waves = 0;
 
@@ -121,12 +121,12 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         if (primary) {
             const int tx = tile % cfg.tiles_x, ty = tile / cfg.tiles_x;
             const int x = tx * 32 + (warp & 3) * 8 + (lane & 7);
-            const int lrow = ty * TILE_ROWS + (warp >> 2) * 4 + (lane >> 3);
+            const int lrow = f.row0 + ty * TILE_ROWS + (warp >> 2) * 4 + (lane >> 3);
             const int y = local_to_image_row(lrow, f.strip_rows, f.rank, f.world);
-            const bool in_buf = x < f.width && lrow < f.local_rows;
+            const bool in_buf = x < f.width && lrow < f.row0 + f.rows && lrow < f.local_rows;
             active = in_buf && y < f.height;
-            pixel = lrow * f.width + x;
-            if (in_buf && !active) f.out[pixel] = make_uchar4(0, 0, 0, 0);   // padding row past the image
+            pixel = (int) out_index(f, lrow, y, x);
+            if (in_buf && !active && !f.direct) f.out[pixel] = make_uchar4(0, 0, 0, 0);   // padding row past the image
             if (active) {
                 o = cam_origin;
                 d = primary_dir(f, cam_origin, x, y);
@@ -304,7 +304,7 @@ cudaError_t launch_wave_variant(const SceneView &scene, const FrameParams &frame
     }
     const size_t smem = wave_fixed_smem<W>() + scene_smem;
     cfg.tiles_x = (frame.width + 31) / 32;
-    cfg.tiles_y = (frame.local_rows + W / 32 - 1) / (W / 32);
+    cfg.tiles_y = (frame.rows + W / 32 - 1) / (W / 32);
     int per_sm = 1;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W, smem);
     if (e != cudaSuccess) return e;

@@ -37,6 +37,7 @@ extern "C" {
 #define RT_B200_OBJECT_BYTES 176 /* sizeof(Object),      include/scene.h:8-15  */
 #define RT_B200_LIGHT_BYTES 48   /* sizeof(LightSource), include/light.h:6-13  */
 #define RT_B200_UNIQUE_ID_BYTES 128
+#define RT_B200_IPC_HANDLE_BYTES 64
 
 typedef struct rt_b200_ctx rt_b200_ctx;
 
@@ -85,6 +86,14 @@ int rt_b200_update(rt_b200_ctx *ctx, const double camera_matrix[16], float *elap
  * With world_size > 1 and no communicator attached only this rank's rows are valid. */
 int rt_b200_gather(rt_b200_ctx *ctx, void *host_rgba8, size_t host_bytes, const void **device_rgba8);
 
+/* update() and the result sink in one call, for hosts that want the frame in host memory every frame (what the
+ * reference's CPU back-end hands to glTexImage2D, update-cpu.cpp:136-137).  On one GPU the frame is rendered in row
+ * bands and each finished band is copied to host_rgba8 on a second stream while the next band renders, so the
+ * device->host transfer overlaps the rendering; *elapsed_ms then covers launch -> last byte on the host.  With
+ * world_size > 1 it is rt_b200_update followed by rt_b200_gather.  host_rgba8 should be page-locked for the overlap. */
+int rt_b200_update_to_host(rt_b200_ctx *ctx, const double camera_matrix[16], void *host_rgba8, size_t host_bytes,
+                           float *elapsed_ms);
+
 /* == cleanup_update(), update.h:8. */
 int rt_b200_destroy(rt_b200_ctx *ctx);
 
@@ -96,16 +105,30 @@ const char *rt_b200_last_error(void);
 int rt_b200_comm_unique_id(void *id_out /* RT_B200_UNIQUE_ID_BYTES */);
 int rt_b200_comm_init(rt_b200_ctx *ctx, const void *id /* RT_B200_UNIQUE_ID_BYTES */);
 
+/* Fused gather (optional, after rt_b200_comm_init): instead of all-gathering packed strips, every rank's render
+ * kernel stores its pixels straight into ONE assembled frame that lives on rank 0 (double-buffered), through a CUDA
+ * IPC mapping over NVLink; a 4-byte all-reduce is the frame-complete barrier.  Rank 0 exports, the host hands the
+ * 64 bytes to every rank, and every rank (rank 0 included) attaches.  Afterwards rt_b200_gather returns rank 0's
+ * frame on every rank (a peer-memory pointer on ranks > 0). */
+int rt_b200_frame_export(rt_b200_ctx *ctx, void *handle_out /* RT_B200_IPC_HANDLE_BYTES */);
+int rt_b200_frame_attach(rt_b200_ctx *ctx, const void *handle /* RT_B200_IPC_HANDLE_BYTES */);
+
 /* ---- introspection and tuning -------------------------------------------------------------------- */
 int rt_b200_get_counters(rt_b200_ctx *ctx, rt_b200_counters *out);
 
-/* Options: "kernel"     0 = exact FP64 kernel (thread per pixel), 1 = wavefront kernel (default)
+/* Options: "kernel"     0 = exact FP64 kernel (thread per pixel), 1 = wavefront kernel (default),
+ *                       2 = queue kernel (path records + per-family FP32 sphere tables; falls back to 1 when the
+ *                           scene exceeds its parameter block)
+ *          "host_bands" row bands of rt_b200_update_to_host (0 = automatic, about 4 MB each)
  *          "strip_rows" image rows per strip of the multi-GPU interleave (default 8)
  *          "count"      1 = maintain rt_b200_counters (default), 0 = skip them                       */
 int rt_b200_set_option(rt_b200_ctx *ctx, const char *name, int64_t value);
 
 /* Split timing of the last update, milliseconds: [0] render kernels, [1] gather (all-gather + unpack). */
 int rt_b200_get_timing(rt_b200_ctx *ctx, float out_ms[2]);
+
+/* Kernels launched by the last rt_b200_update / rt_b200_update_to_host on this rank (render + table setup + unpack). */
+int rt_b200_get_launches(rt_b200_ctx *ctx, uint32_t *launches);
 
 /* Structural class counts of the uploaded scene: planes, spheres, quadrics, cubics. */
 int rt_b200_get_class_counts(rt_b200_ctx *ctx, uint32_t out[4]);

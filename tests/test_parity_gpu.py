@@ -166,6 +166,31 @@ def test_edge_cases(pkg, rt, oracle, kernel):
     check(sc, poses=("identity", "pose_a", "pose_b"))
 
 
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_update_to_host_streams_the_same_frame(pkg, rt, scenes_dir, kernel):
+    """rt_b200_update_to_host (banded render, overlapped D2H) delivers exactly the frame update + gather does."""
+    import torch
+    from cuda_ray_tracer_b200 import camera
+    for name, w, h in (("reflection_test", 1920, 1080), ("dingdong", 1001, 563)):
+        sc = _load(pkg, scenes_dir, name, width=w, height=h, max_reflections=4)
+        host = torch.zeros(w * h * 4, dtype=torch.uint8).pin_memory()
+        with rt.Renderer(sc) as r:
+            r.set_option("kernel", kernel)
+            r.update(camera.TEST_POSES["pose_a"])
+            ref = r.gather()
+            c_ref = r.counters()
+            for bands in (0, 1, 3, 16):
+                r.set_option("host_bands", bands)
+                host.zero_()
+                ms = r.update_to_host(camera.TEST_POSES["pose_a"], host.data_ptr(), host.numel())
+                assert ms > 0.0
+                assert np.array_equal(host.numpy().reshape(h, w, 4), ref), (name, bands)
+                c = r.counters()      # the ray census is band-independent (test counts depend on the shadow cache)
+                assert all(c[k] == c_ref[k] for k in ("primary_rays", "reflection_rays", "shadow_rays", "hits", "lit"))
+            with pytest.raises(rt.RtError):
+                r.update_to_host(camera.TEST_POSES["pose_a"], host.data_ptr(), host.numel() - 1)
+
+
 def test_update_h_call_surface(pkg, rt, oracle, scenes_dir):
     """init_update / update / cleanup_update with one global context, as the reference's update.h:6-8."""
     from cuda_ray_tracer_b200 import camera

@@ -1,5 +1,6 @@
-"""torchrun -N ranks: every rank renders its strips, NCCL all-gather inside rt_b200_update, and EVERY rank checks that
-the assembled frame is byte-identical to a single-GPU render of the same frame on its own device."""
+"""torchrun -N ranks: every rank renders its strips and EVERY rank checks that the assembled frame is byte-identical to a
+single-GPU render of the same frame on its own device — for both assembly paths: NCCL all-gather of packed strips, and
+the fused path (kernels store straight into rank 0's frame through CUDA IPC, 4-byte all-reduce as barrier)."""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tools"))
@@ -19,22 +20,33 @@ cases = [("reflection_test", pkg.load_from_file(os.path.join(ROOT, "scenes", "re
          ("synthetic", synth.synthetic_scene(width=480, height=270), 8)]
 for name, sc, strip in cases:
     m = camera.TEST_POSES["pose_a"]
-    r = binding.Renderer(sc, device=local, rank=rank, world_size=world)
-    r.set_option("strip_rows", strip)
-    ident = [binding.comm_unique_id() if rank == 0 else None]
-    dist.broadcast_object_list(ident, src=0)
-    r.comm_init(ident[0])
-    for _ in range(3):
-        ms = r.update(m)
-    multi = r.gather()
-    t = r.timing()
     single = binding.Renderer(sc, device=local)
     ms1 = min(single.update(m) for _ in range(3))
-    same = bool(np.array_equal(multi, single.gather()))
-    ok &= same
-    print("rank {} {} world {} strips {}: identical={} multi {:.3f} ms (render {:.3f} gather {:.3f}) single {:.3f} ms".format(
-        rank, name, world, strip, same, ms, t["render_ms"], t["gather_ms"], ms1), flush=True)
-    r.close(); single.close()
+    ref = single.gather()
+    single.close()
+    for mode in ("nccl", "p2p"):
+        r = binding.Renderer(sc, device=local, rank=rank, world_size=world)
+        r.set_option("strip_rows", strip)
+        ident = [binding.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ident, src=0)
+        r.comm_init(ident[0])
+        if mode == "p2p":
+            handle = [r.frame_export() if rank == 0 else None]
+            dist.broadcast_object_list(handle, src=0)
+            r.frame_attach(handle[0])
+        same = True
+        for i in range(4):      # several frames: the shared frame is double-buffered
+            ms = r.update(camera.TEST_POSES["pose_b" if i % 2 else "pose_a"])
+        ms = r.update(m)
+        multi = r.gather()
+        dist.barrier()          # nobody starts the next frame while a peer still reads this one
+        t = r.timing()
+        same = bool(np.array_equal(multi, ref))
+        ok &= same
+        print("rank {} {} world {} strips {} {}: identical={} multi {:.3f} ms (render {:.3f} gather {:.3f}) single {:.3f} ms".format(
+            rank, name, world, strip, mode, same, ms, t["render_ms"], t["gather_ms"], ms1), flush=True)
+        r.close()
+        dist.barrier()
 flag = torch.tensor([1 if ok else 0], device="cuda")
 dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 dist.destroy_process_group()
