@@ -339,7 +339,7 @@ def run_b200(args):
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": args.workload, "description": desc, "frames_per_step": len(renderers),
                        "rays_per_step": rays_step, "kernel": args.kernel,
-                       "parallelism": "strips{}x{}rows,{}".format(world, args.strip_rows, "p2p-store+barrier" if fused else
+                       "parallelism": "strips{}x{}rows,{}".format(world, args.strip_rows, "p2p-store+flags" if fused else
                                                                   "nccl-allgather") if world > 1 else "1gpu",
                        "timing": "CUDA events on the render stream per frame, summed; max over ranks",
                        "l2": "outputs ({} MB per step) exceed the 126 MB L2; the scene (KBs) is cache-resident by design"

@@ -27,7 +27,8 @@ COUNTER_FIELDS = ("primary_rays", "reflection_rays", "shadow_rays", "hits", "lit
 EXPORTS = ("rt_b200_upload_scene", "rt_b200_update", "rt_b200_gather", "rt_b200_destroy", "rt_b200_last_error",
            "rt_b200_comm_unique_id", "rt_b200_comm_init", "rt_b200_get_counters", "rt_b200_set_option",
            "rt_b200_get_timing", "rt_b200_get_class_counts", "rt_b200_strip_layout", "rt_b200_version",
-           "rt_b200_update_to_host", "rt_b200_frame_export", "rt_b200_frame_attach", "rt_b200_get_launches")
+           "rt_b200_update_to_host", "rt_b200_frame_export", "rt_b200_frame_attach", "rt_b200_get_launches",
+           "rt_b200_host_alloc", "rt_b200_host_free")
 
 UNIQUE_ID_BYTES = 128
 IPC_HANDLE_BYTES = 64
@@ -70,6 +71,8 @@ def load_library():
     L.rt_b200_frame_export.argtypes = [vp, vp]
     L.rt_b200_frame_attach.argtypes = [vp, vp]
     L.rt_b200_get_launches.argtypes = [vp, C.POINTER(C.c_uint32)]
+    L.rt_b200_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
+    L.rt_b200_host_free.argtypes = [vp]
     L.rt_b200_strip_layout.argtypes = [C.c_uint32, C.c_uint32, C.c_int, C.c_int, vp, C.c_size_t, C.POINTER(C.c_uint32)]
     _lib = L
     return L

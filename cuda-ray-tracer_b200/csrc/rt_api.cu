@@ -143,6 +143,12 @@ struct rt_b200_ctx {
     bool shared_owner = false, shared_ready = false;
     int parity = 0;
     int *d_barrier = nullptr;
+    // sequence words behind the two frames in rank 0's allocation: flags[rank] = last frame this rank finished,
+    // go = last frame rank 0 started (back-pressure: rank r starts frame k only when go >= k - 1)
+    unsigned *d_flags = nullptr, *d_go = nullptr;
+    unsigned *h_timed_out = nullptr, *d_timed_out = nullptr;   // page-locked, mapped: the wait kernel's timeout report
+    unsigned seq = 0;
+    int flag_barrier = 1;            // 1: flag words (default), 0: 4-byte NCCL all-reduce
     const uchar4 *last_frame = nullptr;   // what rt_b200_gather hands out
 
     cudaStream_t stream = nullptr, copy_stream = nullptr;
@@ -356,6 +362,11 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     up(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking), "copy stream");
     for (int b = 0; b < RT_MAX_BANDS; b++) up(cudaEventCreateWithFlags(&c->ev_band[b], cudaEventDisableTiming), "event");
     up(cudaMalloc((void **) &c->d_barrier, sizeof(int)), "barrier word");
+    up(cudaHostAlloc((void **) &c->h_timed_out, sizeof(unsigned), cudaHostAllocMapped), "timeout word");
+    if (c->h_timed_out) {
+        *c->h_timed_out = 0;
+        up(cudaHostGetDevicePointer((void **) &c->d_timed_out, c->h_timed_out, 0), "timeout word");
+    }
     if (rc != RT_B200_OK) {
         rt_b200_destroy(c);
         return rc;
@@ -482,6 +493,11 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
 
     if (c->count) CUDA_TRY(cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long) * rt::CNT_COUNT, c->stream));
     CUDA_TRY(cudaEventRecord(c->ev_start, c->stream));
+    if (shared && c->flag_barrier) {
+        c->seq++;
+        if (c->rank == 0) CUDA_TRY(rt::launch_sync_store(c->d_go, c->seq, c->stream));
+        else CUDA_TRY(rt::launch_sync_wait(c->d_go, 0, 1, c->seq - 1, c->d_timed_out, c->stream));
+    }
     if (c->kernel_kind == 2 && c->qscene)   // the primary-ray table depends on the camera origin: one setup launch per frame
         CUDA_TRY(rt::build_queue_tables(c->view, c->qtables, *c->qscene, 1, 2, f.origin, c->stream));
     c->launches = 0;
@@ -503,8 +519,15 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
     CUDA_TRY(cudaEventRecord(c->ev_render, c->stream));
     c->last_frame = c->d_local;
     if (c->world > 1 && c->comm) {
-        if (shared) {
-            // every rank's pixels are already in rank 0's frame; the 4-byte all-reduce is the frame-complete barrier
+        if (shared && c->flag_barrier) {
+            // every rank's pixels are already in rank 0's frame: each rank publishes "frame seq done" in rank 0's
+            // memory, and only rank 0 — the consumer of the frame — waits for all of them
+            CUDA_TRY(rt::launch_sync_store(c->d_flags + c->rank, c->seq, c->stream));
+            if (c->rank == 0) CUDA_TRY(rt::launch_sync_wait(c->d_flags, 1, c->world - 1, c->seq, c->d_timed_out, c->stream));
+            c->last_frame = c->d_shared[c->parity];
+        }
+        else if (shared) {
+            // same, with a 4-byte all-reduce as the frame-complete barrier (every rank waits for every rank)
             NCCL_TRY(g_nccl.AllReduce(c->d_barrier, c->d_barrier, 1, ncclInt, ncclSum, c->comm, c->stream));
             c->last_frame = c->d_shared[c->parity];
         }
@@ -528,6 +551,9 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
     }
     CUDA_TRY(cudaEventSynchronize(c->ev_end));
     CUDA_TRY(cudaGetLastError());
+    if (shared && c->flag_barrier) {
+        if (*static_cast<volatile unsigned *>(c->h_timed_out)) return fail(RT_B200_ERR_STATE, "a peer rank did not finish its part of the frame (sync timeout)");
+    }
     CUDA_TRY(cudaEventElapsedTime(&c->ms_render, c->ev_start, c->ev_render));
     CUDA_TRY(cudaEventElapsedTime(&c->ms_gather, c->ev_render, c->ev_end));
     float total = c->ms_render + c->ms_gather;
@@ -554,6 +580,20 @@ int rt_b200_update_to_host(rt_b200_ctx *c, const double camera_matrix[16], void 
     return render_frame(c, camera_matrix, host_rgba8, host_bytes, elapsed_ms);
 }
 
+int rt_b200_host_alloc(void **ptr_out, size_t bytes)
+{
+    if (!ptr_out || bytes == 0) return fail(RT_B200_ERR_ARG, "bad host allocation request");
+    *ptr_out = nullptr;
+    CUDA_TRY(cudaHostAlloc(ptr_out, bytes, cudaHostAllocPortable));
+    return RT_B200_OK;
+}
+
+int rt_b200_host_free(void *ptr)
+{
+    if (ptr) CUDA_TRY(cudaFreeHost(ptr));
+    return RT_B200_OK;
+}
+
 int rt_b200_frame_export(rt_b200_ctx *c, void *handle_out)
 {
     if (!c || !handle_out) return fail(RT_B200_ERR_ARG, "null argument");
@@ -562,8 +602,8 @@ int rt_b200_frame_export(rt_b200_ctx *c, void *handle_out)
     static_assert(sizeof(cudaIpcMemHandle_t) == RT_B200_IPC_HANDLE_BYTES, "cudaIpcMemHandle_t size");
     const size_t px = (size_t) c->width * c->height;
     if (!c->d_shared_base) {
-        CUDA_TRY(cudaMalloc((void **) &c->d_shared_base, 2 * sizeof(uchar4) * px));
-        CUDA_TRY(cudaMemset(c->d_shared_base, 0, 2 * sizeof(uchar4) * px));
+        CUDA_TRY(cudaMalloc((void **) &c->d_shared_base, 2 * sizeof(uchar4) * px + 4096));
+        CUDA_TRY(cudaMemset(c->d_shared_base, 0, 2 * sizeof(uchar4) * px + 4096));
         c->shared_owner = true;
     }
     if (!c->shared_owner) return fail(RT_B200_ERR_STATE, "this context maps another rank's frame");
@@ -589,6 +629,10 @@ int rt_b200_frame_attach(rt_b200_ctx *c, const void *handle)
     }
     c->d_shared[0] = c->d_shared_base;
     c->d_shared[1] = c->d_shared_base + px;
+    if (c->world > 1000) return fail(RT_B200_ERR_ARG, "too many ranks for the sync words");
+    c->d_flags = reinterpret_cast<unsigned *>(c->d_shared_base + 2 * px);   // [world] + go
+    c->d_go = c->d_flags + 1000;
+    c->seq = 0;
     c->shared_ready = true;
     CUDA_TRY(cudaMemset(c->d_barrier, 0, sizeof(int)));
     return RT_B200_OK;
@@ -650,6 +694,7 @@ int rt_b200_destroy(rt_b200_ctx *c)
         if (c->ev_band[b]) cudaEventDestroy(c->ev_band[b]);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     cudaFree(c->d_barrier);
+    if (c->h_timed_out) cudaFreeHost(c->h_timed_out);
     if (c->d_shared_base) {
         if (c->shared_owner) cudaFree(c->d_shared_base);
         else cudaIpcCloseMemHandle(c->d_shared_base);
@@ -719,6 +764,9 @@ int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
         if (value < -1 || value > 1) return fail(RT_B200_ERR_ARG, "shadow_cache must be -1, 0 or 1");
         c->shadow_cache = (int) value;
     }
+    else if (!std::strcmp(name, "flag_barrier")) {
+        c->flag_barrier = value != 0;
+    }
     else if (!std::strcmp(name, "host_bands")) {
         if (value < 0 || value > RT_MAX_BANDS) return fail(RT_B200_ERR_ARG, "host_bands must be 0..%d", RT_MAX_BANDS);
         c->host_bands = (int) value;
@@ -764,6 +812,7 @@ int rt_b200_get_launches(rt_b200_ctx *c, uint32_t *launches)
     uint32_t n = (uint32_t) c->launches;
     if (c->kernel_kind == 2 && c->qscene && c->view.n_sphere > 0) n += 1;   // primary-ray table
     if (c->world > 1 && c->comm && !c->shared_ready) n += 1;                 // strip un-interleave
+    if (c->world > 1 && c->comm && c->shared_ready && c->flag_barrier) n += c->rank == 0 ? 3 : 2;   // sequence words
     *launches = n;
     return RT_B200_OK;
 }

@@ -108,6 +108,48 @@ cudaError_t launch_unpack_strips(const uchar4 *gathered, uchar4 *frame, int widt
     return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Frame-complete signalling for the fused gather (one process per GPU, flags in rank 0's memory, mapped by
+// every rank through CUDA IPC).  A kernel boundary orders a rank's pixel stores before its flag store.
+// ---------------------------------------------------------------------------------------------------
+__global__ void sync_store_kernel(unsigned *word, unsigned value)
+{
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(word), "r"(value) : "memory");
+}
+
+// Spin until every word[i], i in [first, first + n), has reached `need` (sequence numbers only grow); gives up
+// after ~20 s of GPU clock and reports through *timed_out, so a dead peer cannot hang the box.
+__global__ void sync_wait_kernel(const unsigned *words, int first, int n, unsigned need, unsigned *timed_out)
+{
+    const long long t0 = clock64();
+    for (int i = first + threadIdx.x; i < first + n; i += blockDim.x) {
+        unsigned v;
+        for (;;) {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(words + i) : "memory");
+            if ((int) (v - need) >= 0) break;
+            if (clock64() - t0 > 40000000000LL) {
+                *timed_out = 1u;
+                break;
+            }
+            __nanosleep(200);
+        }
+    }
+}
+
+cudaError_t launch_sync_store(unsigned *word, unsigned value, cudaStream_t stream)
+{
+    sync_store_kernel<<<1, 1, 0, stream>>>(word, value);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sync_wait(const unsigned *words, int first, int n, unsigned need, unsigned *timed_out, cudaStream_t stream)
+{
+    if (n <= 0) return cudaSuccess;
+    sync_wait_kernel<<<1, 32, 0, stream>>>(words, first, n, need, timed_out);
+    return cudaGetLastError();
+}
+
 int render_launch_count(int kernel_kind)
 {
     (void) kernel_kind;

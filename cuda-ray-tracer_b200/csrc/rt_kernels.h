@@ -50,6 +50,10 @@ cudaError_t launch_render_queue(const SceneView &scene, const FrameParams &frame
 cudaError_t launch_unpack_strips(const uchar4 *gathered, uchar4 *frame, int width, int height, int strip_rows,
                                  int world, int local_rows, cudaStream_t stream);
 
+// Fused-gather signalling through sequence words in peer-mapped memory (rt_kernels.cu).
+cudaError_t launch_sync_store(unsigned *word, unsigned value, cudaStream_t stream);
+cudaError_t launch_sync_wait(const unsigned *words, int first, int n, unsigned need, unsigned *timed_out, cudaStream_t stream);
+
 // Number of kernels a call to launch_render_* enqueues (for bench.py's gpu_launches accounting).
 int render_launch_count(int kernel_kind);
 

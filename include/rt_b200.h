@@ -94,6 +94,11 @@ int rt_b200_gather(rt_b200_ctx *ctx, void *host_rgba8, size_t host_bytes, const 
 int rt_b200_update_to_host(rt_b200_ctx *ctx, const double camera_matrix[16], void *host_rgba8, size_t host_bytes,
                            float *elapsed_ms);
 
+/* Page-locked host memory for frames (so that the streamed copy above really overlaps); plain C, no CUDA headers
+ * needed by the host.  rt_b200_host_free(NULL) is a no-op. */
+int rt_b200_host_alloc(void **ptr_out, size_t bytes);
+int rt_b200_host_free(void *ptr);
+
 /* == cleanup_update(), update.h:8. */
 int rt_b200_destroy(rt_b200_ctx *ctx);
 

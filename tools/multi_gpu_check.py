@@ -24,13 +24,14 @@ for name, sc, strip in cases:
     ms1 = min(single.update(m) for _ in range(3))
     ref = single.gather()
     single.close()
-    for mode in ("nccl", "p2p"):
+    for mode in ("nccl", "p2p-allreduce", "p2p"):
         r = binding.Renderer(sc, device=local, rank=rank, world_size=world)
         r.set_option("strip_rows", strip)
         ident = [binding.comm_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ident, src=0)
         r.comm_init(ident[0])
-        if mode == "p2p":
+        if mode != "nccl":
+            r.set_option("flag_barrier", 1 if mode == "p2p" else 0)
             handle = [r.frame_export() if rank == 0 else None]
             dist.broadcast_object_list(handle, src=0)
             r.frame_attach(handle[0])
@@ -38,6 +39,8 @@ for name, sc, strip in cases:
         for i in range(4):      # several frames: the shared frame is double-buffered
             ms = r.update(camera.TEST_POSES["pose_b" if i % 2 else "pose_a"])
         ms = r.update(m)
+        if mode == "p2p":
+            dist.barrier()      # flag words: only rank 0 waits for every rank; the others need a host barrier to read
         multi = r.gather()
         dist.barrier()          # nobody starts the next frame while a peer still reads this one
         t = r.timing()
