@@ -57,6 +57,16 @@ def load_peaks() -> dict:
     return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0, "_source": "fallback"}
 
 
+def measured_traffic():
+    """dram__bytes_read + dram__bytes_write per launch of the render kernel, from the committed ncu capture."""
+    path = os.path.join(ROOT, "profiles", "r1_traffic.json")
+    try:
+        with open(path) as f:
+            return int(json.load(f)["dram_bytes_per_launch"])
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def fp32_peak_tflops(n_sms: int, sm_mhz: float) -> float:
     """FP32 SIMT peak: SMs x 128 lanes x 2 flop (FMA) x clock."""
     return n_sms * 128 * 2 * sm_mhz * 1e6 / 1e12
@@ -352,7 +362,7 @@ def run_b200(args):
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s",
-                         "frac": achieved / fp32_peak, "traffic": None,
+                         "frac": achieved / fp32_peak, "traffic": measured_traffic(),
                          "peak_source": "148 SMs x 128 lanes x 2 x sm_max_mhz of MEASURED_PEAKS.json ({})".format(peaks["_source"]),
                          "algorithmic_gflop_per_step": flops_step / 1e9, "kernel_ms_per_step": render_ms_sum,
                          "blended": {"frac": t_min_ms / render_ms_sum, "fp32_gflop": fl32 / 1e9, "fp64_gflop": fl64 / 1e9,
@@ -392,7 +402,8 @@ def cpu_baseline(pkg, scenes, args) -> dict:
             _, ms = oracle_py.PortOracle(sc).render_rows(m, 0, sc.px_height, ystep, threads=cores)
         secs += ms / 1e3
     return {"value": rays / secs / 1e6, "unit": UNIT, "cores": cores, "kind": kind,
-            "sample": "every {}th image row of each frame of the workload, {} host threads, {:.1f} s".format(ystep, cores, secs)}
+            "sample": "{} of each frame of the workload, {} host threads, {:.1f} s".format(
+                "every image row" if ystep == 1 else "every {}th image row".format(ystep), cores, secs)}
 
 
 def main():
