@@ -245,6 +245,15 @@ def run_b200(args):
     frame_bytes = max(sc.px_width * sc.px_height * 4 for _, sc in scenes)
     host_frame = torch.empty(frame_bytes, dtype=torch.uint8).pin_memory()
     host_cam = torch.from_numpy(m.copy()).pin_memory()
+    shared_ptr = 0
+    if world > 1 and args.e2e == "shared":
+        # one host frame mapped (and page-locked) by every rank: each GPU's copy engine delivers its own strips
+        path = [binding.shared_frame_path(frame_bytes) if rank == 0 else None]
+        if rank == 0:
+            shared_ptr = binding.host_alloc_shared(path[0], frame_bytes, True)
+        dist.broadcast_object_list(path, src=0)
+        if rank != 0:
+            shared_ptr = binding.host_alloc_shared(path[0], frame_bytes, False)
 
     def step_e2e():
         """The user-facing call with HOST buffers: camera matrix in, finished frame in pinned host memory out."""
@@ -252,6 +261,8 @@ def run_b200(args):
             nbytes = sc.px_width * sc.px_height * 4
             if world == 1:
                 r.update_to_host(host_cam.numpy(), host_frame.data_ptr(), nbytes)
+            elif shared_ptr:
+                r.update_to_host(host_cam.numpy(), shared_ptr, nbytes)
             else:
                 r.update(host_cam.numpy())
                 if rank == 0:           # the frame is assembled on GPU 0 (north_star); rank 0 hands it to the host
@@ -357,7 +368,10 @@ def run_b200(args):
             "e2e": {"value": rays_step / ms_e2e / 1e3, "unit": UNIT, "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": len(renderers) * 128,
                     "how": "rt_b200_update_to_host: banded render with the D2H copy of finished bands overlapped"
-                           if world == 1 else "rt_b200_update on every rank + rt_b200_gather to pinned host memory on rank 0",
+                           if world == 1 else
+                           "rt_b200_update_to_host on every rank into one shared page-locked host frame: each GPU copies its own strips over its own PCIe link"
+                           if args.e2e == "shared" else
+                           "rt_b200_update on every rank + rt_b200_gather to pinned host memory on rank 0",
                     "d2h_bytes_per_step": int(sum(sc.px_width * sc.px_height * 4 for _, sc, _ in renderers))},
             "gpu_launches": launches,
             "clocks": clocks,
@@ -379,6 +393,9 @@ def run_b200(args):
 
     for _, _, r in renderers:
         r.close()
+    if shared_ptr:
+        barrier()
+        binding.host_free_shared(shared_ptr)
     if world > 1:
         dist.destroy_process_group()
 
@@ -418,6 +435,8 @@ def main():
     ap.add_argument("--ref-row-step", type=int, default=0, help="CPU legs render every n-th image row (0 = 1 for the "
                     "cpu_baseline leg, 2 for --impl reference steps)")
     ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"], help="multi-GPU frame assembly")
+    ap.add_argument("--e2e", default="shared", choices=["shared", "gather"], help="multi-GPU end-to-end leg: every rank "
+                    "copies its strips into one shared host frame, or rank 0 gathers on the device and copies alone")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -28,7 +28,7 @@ EXPORTS = ("rt_b200_upload_scene", "rt_b200_update", "rt_b200_gather", "rt_b200_
            "rt_b200_comm_unique_id", "rt_b200_comm_init", "rt_b200_get_counters", "rt_b200_set_option",
            "rt_b200_get_timing", "rt_b200_get_class_counts", "rt_b200_strip_layout", "rt_b200_version",
            "rt_b200_update_to_host", "rt_b200_frame_export", "rt_b200_frame_attach", "rt_b200_get_launches",
-           "rt_b200_host_alloc", "rt_b200_host_free")
+           "rt_b200_host_alloc", "rt_b200_host_free", "rt_b200_host_alloc_shared", "rt_b200_host_free_shared")
 
 UNIQUE_ID_BYTES = 128
 IPC_HANDLE_BYTES = 64
@@ -73,6 +73,8 @@ def load_library():
     L.rt_b200_get_launches.argtypes = [vp, C.POINTER(C.c_uint32)]
     L.rt_b200_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
     L.rt_b200_host_free.argtypes = [vp]
+    L.rt_b200_host_alloc_shared.argtypes = [C.c_char_p, C.c_size_t, C.c_int, C.POINTER(vp)]
+    L.rt_b200_host_free_shared.argtypes = [vp]
     L.rt_b200_strip_layout.argtypes = [C.c_uint32, C.c_uint32, C.c_int, C.c_int, vp, C.c_size_t, C.POINTER(C.c_uint32)]
     _lib = L
     return L
@@ -101,6 +103,37 @@ def comm_unique_id() -> bytes:
     buf = (C.c_char * UNIQUE_ID_BYTES)()
     _check(load_library().rt_b200_comm_unique_id(buf))
     return bytes(buf)
+
+
+def shared_frame_path(nbytes: int) -> str:
+    """A fresh path for rt_b200_host_alloc_shared: /dev/shm when it has room, else the temp directory."""
+    import shutil
+    import tempfile
+    import uuid
+    root = "/dev/shm"
+    try:
+        if shutil.disk_usage(root).free < nbytes + (1 << 20):
+            root = tempfile.gettempdir()
+    except OSError:
+        root = tempfile.gettempdir()
+    return os.path.join(root, "rt_b200_{}_{}".format(os.getpid(), uuid.uuid4().hex[:8]))
+
+
+def host_alloc_shared(path: str, nbytes: int, create: bool) -> int:
+    """Host frame shared by all ranks of a multi-GPU job (one rank creates, the others open); returns the address."""
+    p = C.c_void_p()
+    _check(load_library().rt_b200_host_alloc_shared(path.encode(), nbytes, 1 if create else 0, C.byref(p)))
+    return int(p.value)
+
+
+def host_free_shared(ptr: int):
+    _check(load_library().rt_b200_host_free_shared(C.c_void_p(ptr)))
+
+
+def host_view(ptr: int, height: int, width: int) -> np.ndarray:
+    """uint8 [H, W, 4] view of a host frame at `ptr` (no copy)."""
+    buf = (C.c_uint8 * (height * width * 4)).from_address(ptr)
+    return np.frombuffer(buf, dtype=np.uint8).reshape(height, width, 4)
 
 
 class Renderer:

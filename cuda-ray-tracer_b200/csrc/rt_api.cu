@@ -9,13 +9,21 @@
 // No CPU rendering path exists in this library: if CUDA is unavailable the calls fail with RT_B200_ERR_CUDA.
 #include <cuda_runtime.h>
 #include <dlfcn.h>
+#include <fcntl.h>
 #include <nccl.h>
+#include <sched.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <time.h>
+#include <unistd.h>
 
+#include <cerrno>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <algorithm>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -82,6 +90,58 @@ int load_nccl()
         ncclResult_t r_ = (expr);                                                                      \
         if (r_ != ncclSuccess) return fail(RT_B200_ERR_NCCL, "%s: %s", #expr, g_nccl.GetErrorString(r_)); \
     } while (0)
+
+// ---- host frames shared between the processes of a multi-GPU job -------------------------------------
+// A file-backed MAP_SHARED mapping (the caller picks the path, normally under /dev/shm), page-locked in every
+// process that maps it, so each rank's copy engine writes its own strips of the frame straight into the one host
+// buffer the consumer reads: G PCIe links fill one frame.  Behind the frame sits one page of sequence words:
+//   go        last frame rank 0 (the consumer) has entered — rank r may overwrite the buffer for frame k once go >= k
+//   done[r]   last frame whose strips rank r has finished copying
+struct SharedTrailer {
+    unsigned go;
+    unsigned pad[15];
+    unsigned done[1000];
+};
+static_assert(sizeof(SharedTrailer) <= 4096, "one page of sync words");
+
+struct SharedBlock {
+    void *base = nullptr;
+    size_t bytes = 0, mapped = 0;
+    std::string path;
+    bool creator = false;
+    unsigned seq = 0;   // frames this process has sent through the block
+    SharedTrailer *trailer() const { return reinterpret_cast<SharedTrailer *>(static_cast<char *>(base) + mapped - 4096); }
+};
+std::mutex g_blocks_mutex;
+std::vector<SharedBlock *> g_blocks;
+
+SharedBlock *find_block(const void *p)
+{
+    std::lock_guard<std::mutex> lock(g_blocks_mutex);
+    for (SharedBlock *b : g_blocks)
+        if (b->base == p) return b;
+    return nullptr;
+}
+
+double now_seconds()
+{
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (double) ts.tv_sec + 1e-9 * (double) ts.tv_nsec;
+}
+
+// spin until *word >= need (acquire); false after `timeout_s`
+bool host_wait_word(const unsigned *word, unsigned need, double timeout_s)
+{
+    const double t0 = now_seconds();
+    for (unsigned spins = 0;; spins++) {
+        if ((int) (__atomic_load_n(word, __ATOMIC_ACQUIRE) - need) >= 0) return true;
+        if ((spins & 1023) == 1023) {
+            if (now_seconds() - t0 > timeout_s) return false;
+            sched_yield();
+        }
+    }
+}
 
 template <typename T>
 cudaError_t upload(const std::vector<T> &host, T **dev)
@@ -469,7 +529,11 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
     f.row0 = 0;
     f.rows = c->local_rows;
     f.counters = c->count ? c->d_counters : nullptr;
-    const bool shared = c->world > 1 && c->comm && c->shared_ready;
+    // host frame shared by all ranks (rt_b200_host_alloc_shared): every rank copies its own strips to the host
+    SharedBlock *blk = (host_sink && c->world > 1) ? find_block(host_sink) : nullptr;
+    if (blk && blk->bytes < frame_bytes)
+        return fail(RT_B200_ERR_ARG, "shared host block holds %zu bytes, frame needs %zu", blk->bytes, frame_bytes);
+    const bool shared = c->world > 1 && c->comm && c->shared_ready && !blk;
     if (shared) {
         c->parity ^= 1;                 // rank 0 may still be reading the previous frame: write the other buffer
         f.out = c->d_shared[c->parity];
@@ -480,16 +544,32 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
         f.direct = 0;
     }
 
-    // row bands of the streamed host copy (single GPU only): ~4 MB each, whole 16-row tiles
+    // row bands of the streamed host copy: ~4 MB each, whole 16-row tiles (and whole strips when ranks share the
+    // host frame)
     int n_bands = 1;
-    const bool streamed = host_sink != nullptr && c->world == 1;
+    const bool streamed = host_sink != nullptr && (c->world == 1 || blk);
+    int band_unit = 16;
+    if (blk) {
+        int a = 16, b = c->strip_rows;
+        while (b) { const int t = a % b; a = b; b = t; }
+        band_unit = 16 / a * c->strip_rows;   // lcm(16, strip_rows)
+    }
     if (streamed) {
-        n_bands = c->host_bands > 0 ? c->host_bands : (int) (frame_bytes / (4u << 20));
+        const size_t local_bytes = sizeof(uchar4) * (size_t) c->width * c->local_rows;
+        n_bands = c->host_bands > 0 ? c->host_bands : (int) (local_bytes / (4u << 20));
         if (n_bands > RT_MAX_BANDS) n_bands = RT_MAX_BANDS;
-        if (n_bands > (c->local_rows + 15) / 16) n_bands = (c->local_rows + 15) / 16;
+        if (n_bands > (c->local_rows + band_unit - 1) / band_unit) n_bands = (c->local_rows + band_unit - 1) / band_unit;
         if (n_bands < 1) n_bands = 1;
     }
-    const int band_rows = ((c->local_rows + n_bands - 1) / n_bands + 15) & ~15;
+    const int band_rows = ((c->local_rows + n_bands - 1) / n_bands + band_unit - 1) / band_unit * band_unit;
+    unsigned host_seq = 0;
+    if (blk) {
+        host_seq = ++blk->seq;
+        SharedTrailer *t = blk->trailer();
+        if (c->rank == 0) __atomic_store_n(&t->go, host_seq, __ATOMIC_RELEASE);
+        else if (!host_wait_word(&t->go, host_seq, 20.0))
+            return fail(RT_B200_ERR_STATE, "rank 0 did not enter frame %u of the shared host block (timeout)", host_seq);
+    }
 
     if (c->count) CUDA_TRY(cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long) * rt::CNT_COUNT, c->stream));
     CUDA_TRY(cudaEventRecord(c->ev_start, c->stream));
@@ -512,13 +592,44 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
             CUDA_TRY(cudaEventRecord(c->ev_band[b], c->stream));
             CUDA_TRY(cudaStreamWaitEvent(c->copy_stream, c->ev_band[b], 0));
             const size_t off = (size_t) f.row0 * c->width;
-            CUDA_TRY(cudaMemcpyAsync(static_cast<uchar4 *>(host_sink) + off, c->d_local + off,
-                                     sizeof(uchar4) * (size_t) f.rows * c->width, cudaMemcpyDeviceToHost, c->copy_stream));
+            if (!blk) {
+                CUDA_TRY(cudaMemcpyAsync(static_cast<uchar4 *>(host_sink) + off, c->d_local + off,
+                                         sizeof(uchar4) * (size_t) f.rows * c->width, cudaMemcpyDeviceToHost, c->copy_stream));
+            }
+            else {
+                // local strip s of this rank is image strip s * world + rank: one pitched copy scatters the band's
+                // strips to their image rows; a ragged last strip goes separately; padding strips are not copied
+                const int n_strips = (c->height + c->strip_rows - 1) / c->strip_rows;
+                const int s0 = f.row0 / c->strip_rows, s1 = (f.row0 + f.rows) / c->strip_rows;
+                const size_t strip_bytes = sizeof(uchar4) * (size_t) c->strip_rows * c->width;
+                int full = 0, ragged = -1;
+                for (int sl = s0; sl < s1; sl++) {
+                    const int g = sl * c->world + c->rank;
+                    if (g >= n_strips) break;
+                    if ((g + 1) * c->strip_rows <= c->height) full++;
+                    else ragged = sl;
+                }
+                char *dst = static_cast<char *>(host_sink) + ((size_t) s0 * c->world + c->rank) * strip_bytes;
+                const char *src = reinterpret_cast<const char *>(c->d_local) + (size_t) s0 * strip_bytes;
+                if (full > 0)
+                    CUDA_TRY(cudaMemcpy2DAsync(dst, strip_bytes * c->world, src, strip_bytes, strip_bytes, full,
+                                               cudaMemcpyDeviceToHost, c->copy_stream));
+                if (ragged >= 0) {
+                    const int g = ragged * c->world + c->rank;
+                    const size_t rows = (size_t) c->height - (size_t) g * c->strip_rows;
+                    CUDA_TRY(cudaMemcpyAsync(static_cast<char *>(host_sink) + (size_t) g * strip_bytes,
+                                             reinterpret_cast<const char *>(c->d_local) + (size_t) ragged * strip_bytes,
+                                             sizeof(uchar4) * rows * c->width, cudaMemcpyDeviceToHost, c->copy_stream));
+                }
+            }
         }
     }
     CUDA_TRY(cudaEventRecord(c->ev_render, c->stream));
     c->last_frame = c->d_local;
-    if (c->world > 1 && c->comm) {
+    if (blk) {
+        c->last_frame = nullptr;   // the frame is assembled in host memory; rt_b200_gather would see this rank's rows only
+    }
+    else if (c->world > 1 && c->comm) {
         if (shared && c->flag_barrier) {
             // every rank's pixels are already in rank 0's frame: each rank publishes "frame seq done" in rank 0's
             // memory, and only rank 0 — the consumer of the frame — waits for all of them
@@ -558,6 +669,16 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
     CUDA_TRY(cudaEventElapsedTime(&c->ms_gather, c->ev_render, c->ev_end));
     float total = c->ms_render + c->ms_gather;
     if (streamed) CUDA_TRY(cudaEventElapsedTime(&total, c->ev_start, c->ev_copy));
+    if (blk) {
+        // this rank's strips are in host memory (the event wait above); publish that, and rank 0 — whose caller
+        // reads the frame — waits for every rank
+        SharedTrailer *t = blk->trailer();
+        __atomic_store_n(&t->done[c->rank], host_seq, __ATOMIC_RELEASE);
+        if (c->rank == 0)
+            for (int r = 1; r < c->world; r++)
+                if (!host_wait_word(&t->done[r], host_seq, 20.0))
+                    return fail(RT_B200_ERR_STATE, "rank %d did not deliver its strips of frame %u (timeout)", r, host_seq);
+    }
     c->rendered = true;
     if (elapsed_ms) *elapsed_ms = total;
     if (host_sink && !streamed) return rt_b200_gather(c, host_sink, host_bytes, nullptr);
@@ -591,6 +712,71 @@ int rt_b200_host_alloc(void **ptr_out, size_t bytes)
 int rt_b200_host_free(void *ptr)
 {
     if (ptr) CUDA_TRY(cudaFreeHost(ptr));
+    return RT_B200_OK;
+}
+
+int rt_b200_host_alloc_shared(const char *path, size_t bytes, int create, void **ptr_out)
+{
+    if (!path || !ptr_out || bytes == 0) return fail(RT_B200_ERR_ARG, "bad shared host allocation request");
+    *ptr_out = nullptr;
+    const size_t mapped = ((bytes + 4095) & ~(size_t) 4095) + 4096;
+    const int fd = open(path, create ? (O_RDWR | O_CREAT | O_EXCL) : O_RDWR, 0600);
+    if (fd < 0) return fail(RT_B200_ERR_ARG, "cannot %s %s: %s", create ? "create" : "open", path, std::strerror(errno));
+    if (create && ftruncate(fd, (off_t) mapped) != 0) {   // zero-filled: all sequence words start at 0
+        const int e = errno;
+        close(fd);
+        unlink(path);
+        return fail(RT_B200_ERR_ARG, "cannot size %s to %zu bytes: %s", path, mapped, std::strerror(e));
+    }
+    struct stat st;
+    if (fstat(fd, &st) != 0 || (size_t) st.st_size < mapped) {
+        close(fd);
+        return fail(RT_B200_ERR_ARG, "%s is smaller than the %zu bytes this frame needs", path, mapped);
+    }
+    void *base = mmap(nullptr, mapped, PROT_READ | PROT_WRITE, MAP_SHARED | MAP_POPULATE, fd, 0);
+    close(fd);
+    if (base == MAP_FAILED) {
+        if (create) unlink(path);
+        return fail(RT_B200_ERR_ARG, "cannot map %s: %s", path, std::strerror(errno));
+    }
+    const cudaError_t e = cudaHostRegister(base, mapped, cudaHostRegisterPortable);
+    if (e != cudaSuccess) {
+        munmap(base, mapped);
+        if (create) unlink(path);
+        return fail(RT_B200_ERR_CUDA, "cudaHostRegister(%s): %s", path, cudaGetErrorString(e));
+    }
+    SharedBlock *b = new SharedBlock;
+    b->base = base;
+    b->bytes = bytes;
+    b->mapped = mapped;
+    b->path = path;
+    b->creator = create != 0;
+    {
+        std::lock_guard<std::mutex> lock(g_blocks_mutex);
+        g_blocks.push_back(b);
+    }
+    *ptr_out = base;
+    return RT_B200_OK;
+}
+
+int rt_b200_host_free_shared(void *ptr)
+{
+    if (!ptr) return RT_B200_OK;
+    SharedBlock *b = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_blocks_mutex);
+        for (size_t i = 0; i < g_blocks.size(); i++)
+            if (g_blocks[i]->base == ptr) {
+                b = g_blocks[i];
+                g_blocks.erase(g_blocks.begin() + (long) i);
+                break;
+            }
+    }
+    if (!b) return fail(RT_B200_ERR_ARG, "not a block of rt_b200_host_alloc_shared");
+    cudaHostUnregister(b->base);
+    munmap(b->base, b->mapped);
+    if (b->creator) unlink(b->path.c_str());
+    delete b;
     return RT_B200_OK;
 }
 

@@ -89,8 +89,14 @@ int rt_b200_gather(rt_b200_ctx *ctx, void *host_rgba8, size_t host_bytes, const 
 /* update() and the result sink in one call, for hosts that want the frame in host memory every frame (what the
  * reference's CPU back-end hands to glTexImage2D, update-cpu.cpp:136-137).  On one GPU the frame is rendered in row
  * bands and each finished band is copied to host_rgba8 on a second stream while the next band renders, so the
- * device->host transfer overlaps the rendering; *elapsed_ms then covers launch -> last byte on the host.  With
- * world_size > 1 it is rt_b200_update followed by rt_b200_gather.  host_rgba8 should be page-locked for the overlap. */
+ * device->host transfer overlaps the rendering; *elapsed_ms then covers launch -> last byte on the host.
+ * host_rgba8 should be page-locked for the overlap.  With world_size > 1 there are two forms:
+ *   - host_rgba8 from rt_b200_host_alloc_shared (the same block mapped by every rank): every rank renders its strips
+ *     and its own copy engine writes them to their image rows of the one host frame, so G PCIe links fill it in
+ *     parallel and nothing crosses NVLink; all ranks call it for every frame, the frame is complete when RANK 0's
+ *     call returns (the other ranks return when their own strips are out), and a rank does not start overwriting
+ *     the block for frame k+1 before rank 0 has entered its call for frame k+1;
+ *   - any other buffer: rt_b200_update followed by rt_b200_gather. */
 int rt_b200_update_to_host(rt_b200_ctx *ctx, const double camera_matrix[16], void *host_rgba8, size_t host_bytes,
                            float *elapsed_ms);
 
@@ -98,6 +104,14 @@ int rt_b200_update_to_host(rt_b200_ctx *ctx, const double camera_matrix[16], voi
  * needed by the host.  rt_b200_host_free(NULL) is a no-op. */
 int rt_b200_host_alloc(void **ptr_out, size_t bytes);
 int rt_b200_host_free(void *ptr);
+
+/* A host frame shared by the processes of a multi-GPU job: a MAP_SHARED mapping of the file `path` (normally under
+ * /dev/shm), page-locked in the calling process.  Exactly one rank passes create != 0 (the file must not exist; it
+ * is sized to `bytes` + one page of synchronisation words and unlinked again when that rank frees the block); the
+ * others open it afterwards with create == 0 and the same `bytes`.  New with the multi-GPU path — the reference is
+ * one process, one GPU. */
+int rt_b200_host_alloc_shared(const char *path, size_t bytes, int create, void **ptr_out);
+int rt_b200_host_free_shared(void *ptr);
 
 /* == cleanup_update(), update.h:8. */
 int rt_b200_destroy(rt_b200_ctx *ctx);

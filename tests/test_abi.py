@@ -78,3 +78,38 @@ def test_argument_errors_and_no_gpu(pkg, lib):
             binding.Renderer(sc)
         with pytest.raises(binding.RtError, match="before init_update"):
             binding.update(np.eye(4).reshape(16))
+
+
+def test_shared_host_block_arguments(pkg, lib, tmp_path):
+    """rt_b200_host_alloc_shared: argument checks, and without a GPU the page-lock fails loudly and leaves no file."""
+    from cuda_ray_tracer_b200 import binding
+    p = C.c_void_p()
+    assert lib.rt_b200_host_alloc_shared(None, 4096, 1, C.byref(p)) == 1
+    assert lib.rt_b200_host_alloc_shared(b"/nonexistent-dir/x", 4096, 1, C.byref(p)) == 1
+    assert b"cannot create" in lib.rt_b200_last_error()
+    missing = str(tmp_path / "missing").encode()
+    assert lib.rt_b200_host_alloc_shared(missing, 4096, 0, C.byref(p)) == 1 and b"cannot open" in lib.rt_b200_last_error()
+    assert lib.rt_b200_host_free_shared(None) == 0
+    x = C.c_int(0)
+    assert lib.rt_b200_host_free_shared(C.byref(x)) == 1
+    path = tmp_path / "frame"
+    try:
+        import torch
+        has_gpu = torch.cuda.is_available()
+    except Exception:
+        has_gpu = False
+    if has_gpu:
+        ptr = binding.host_alloc_shared(str(path), 10000, True)
+        with pytest.raises(binding.RtError, match="cannot create"):     # exclusive: a second creator is refused
+            binding.host_alloc_shared(str(path), 10000, True)
+        other = binding.host_alloc_shared(str(path), 10000, False)
+        binding.host_view(ptr, 50, 50)[:] = 7
+        assert int(binding.host_view(other, 50, 50).min()) == 7        # same pages
+        binding.host_free_shared(other)
+        assert path.exists()
+        binding.host_free_shared(ptr)
+        assert not path.exists()                                         # the creator unlinks
+    else:
+        with pytest.raises(binding.RtError, match="rt_b200 error 2"):
+            binding.host_alloc_shared(str(path), 10000, True)
+        assert not path.exists()

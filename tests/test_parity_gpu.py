@@ -221,3 +221,62 @@ def test_reference_build_agrees_on_gpu_box(pkg, rt, oracle, scenes_dir):
         with rt.Renderer(sc) as r:
             r.update(camera.TEST_POSES["pose_a"])
             assert_parity(r.gather(), oracle.quantize_rgba8(rgb), name)
+
+
+def _shared_host_worker(rank, world, path, name, w, h, strip, out_dir):
+    """One rank of test_shared_host_frame_ranks_as_processes (both ranks use cuda:0: the path needs no peer GPU)."""
+    import sys
+    root = os.path.dirname(HERE)
+    for p in (root, os.path.join(root, "tools")):
+        sys.path.insert(0, p)
+    from loader import load_package
+    pkg = load_package()
+    from cuda_ray_tracer_b200 import binding, camera
+    sc = pkg.load_from_file(os.path.join(root, "scenes", name + ".yml")).with_overrides(width=w, height=h, max_reflections=4)
+    ptr = binding.host_alloc_shared(path, w * h * 4, False)
+    ok = True
+    with binding.Renderer(sc, rank=rank, world_size=world) as r:
+        r.set_option("strip_rows", strip)
+        for bands in (0, 1, 2):
+            r.set_option("host_bands", bands)
+            for pose in ("pose_b", "pose_a"):
+                r.update_to_host(camera.TEST_POSES[pose], ptr, w * h * 4)
+                if rank == 0:      # complete when rank 0 returns; nobody overwrites it before rank 0's next call
+                    got = binding.host_view(ptr, h, w).copy()
+                    ok &= bool(np.array_equal(got, np.load(os.path.join(out_dir, pose + ".npy"))))
+    binding.host_free_shared(ptr)
+    with open(os.path.join(out_dir, "rank{}.txt".format(rank)), "w") as f:
+        f.write("ok" if ok else "mismatch")
+
+
+@pytest.mark.parametrize("world,strip", [(2, 8), (3, 5)])
+def test_shared_host_frame_ranks_as_processes(pkg, rt, scenes_dir, tmp_path, world, strip):
+    """Multi-rank rt_b200_update_to_host into one shared host frame: every rank (a process) copies its own strips to
+    their image rows; rank 0 sees the complete frame, byte-identical to the single-rank frame — ragged last strip,
+    padding strips and several bands included."""
+    import torch.multiprocessing as mp
+    from cuda_ray_tracer_b200 import camera
+    name, w, h = "reflection_test", 333, 203
+    sc = _load(pkg, scenes_dir, name, width=w, height=h, max_reflections=4)
+    with rt.Renderer(sc) as r:
+        for pose in ("pose_a", "pose_b"):
+            r.update(camera.TEST_POSES[pose])
+            np.save(tmp_path / (pose + ".npy"), r.gather())
+    path = rt.shared_frame_path(w * h * 4)
+    ptr = rt.host_alloc_shared(path, w * h * 4, True)
+    try:
+        ctx = mp.get_context("spawn")
+        procs = [ctx.Process(target=_shared_host_worker, args=(k, world, path, name, w, h, strip, str(tmp_path)))
+                 for k in range(world)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(timeout=180)
+        assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+        for k in range(world):
+            assert (tmp_path / "rank{}.txt".format(k)).read_text() == "ok"
+    finally:
+        for p in procs:
+            if p.is_alive():
+                p.kill()
+        rt.host_free_shared(ptr)

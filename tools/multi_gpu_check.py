@@ -50,6 +50,30 @@ for name, sc, strip in cases:
             rank, name, world, strip, mode, same, ms, t["render_ms"], t["gather_ms"], ms1), flush=True)
         r.close()
         dist.barrier()
+    # host frame shared by all ranks: every rank's copy engine writes its own strips (no NVLink, no communicator)
+    nbytes = sc.px_width * sc.px_height * 4
+    path = [binding.shared_frame_path(nbytes) if rank == 0 else None]
+    ptr = binding.host_alloc_shared(path[0], nbytes, True) if rank == 0 else 0
+    dist.broadcast_object_list(path, src=0)
+    if rank != 0:
+        ptr = binding.host_alloc_shared(path[0], nbytes, False)
+    for bands in (0, 1, 3):
+        r = binding.Renderer(sc, device=local, rank=rank, world_size=world)
+        r.set_option("strip_rows", strip)
+        r.set_option("host_bands", bands)
+        for i in range(4):
+            r.update_to_host(camera.TEST_POSES["pose_b" if i % 2 else "pose_a"], ptr, nbytes)
+        ms = r.update_to_host(m, ptr, nbytes)
+        same = True
+        if rank == 0:           # the frame is complete when rank 0's call returns
+            same = bool(np.array_equal(binding.host_view(ptr, sc.px_height, sc.px_width), ref))
+        ok &= same
+        print("rank {} {} world {} strips {} host-shared bands {}: identical={} {:.3f} ms".format(
+            rank, name, world, strip, bands, same, ms), flush=True)
+        dist.barrier()          # rank 0 has compared before anybody renders into the block again
+        r.close()
+    dist.barrier()
+    binding.host_free_shared(ptr)
 flag = torch.tensor([1 if ok else 0], device="cuda")
 dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 dist.destroy_process_group()
