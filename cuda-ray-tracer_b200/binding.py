@@ -21,7 +21,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "librt_b200.so")
 
 COUNTER_FIELDS = ("primary_rays", "reflection_rays", "shadow_rays", "hits", "lit",
-                  "tests_plane", "tests_sphere", "tests_quadric", "tests_cubic", "fp64_confirms")
+                  "tests_plane", "tests_sphere", "tests_quadric", "tests_cubic", "fp64_confirms", "cubic_exact")
 
 # every symbol include/rt_b200.h declares
 EXPORTS = ("rt_b200_upload_scene", "rt_b200_update", "rt_b200_gather", "rt_b200_destroy", "rt_b200_last_error",

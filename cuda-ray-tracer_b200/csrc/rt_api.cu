@@ -189,6 +189,7 @@ struct rt_b200_ctx {
     float sphere_r2_max = 0.0f;
     int shadow_cache = -1;
     int wave_variant = 0;
+    int cubic_filter = 1;
     bool buffers_dirty = true;
 
     int kernel_kind = 1;
@@ -492,7 +493,7 @@ int launch_kernel(rt_b200_ctx *c, const rt::FrameParams &f)
         CUDA_TRY(rt::launch_render_queue(c->view, f, ql, c->stream));
     }
     else {   // kernel 1, and kernel 2 for scenes that exceed the queue kernel's parameter block
-        rt::WaveLaunch wl{c->d_tile_counter, c->d_cubic_mask, c->sphere_r2_max, c->shadow_cache, c->wave_variant};
+        rt::WaveLaunch wl{c->d_tile_counter, c->d_cubic_mask, c->sphere_r2_max, c->shadow_cache, c->wave_variant, c->cubic_filter};
         CUDA_TRY(rt::launch_render_wave(c->view, f, wl, c->stream));
     }
     return RT_B200_OK;
@@ -952,6 +953,9 @@ int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
     }
     else if (!std::strcmp(name, "flag_barrier")) {
         c->flag_barrier = value != 0;
+    }
+    else if (!std::strcmp(name, "cubic_filter")) {
+        c->cubic_filter = value ? 1 : 0;
     }
     else if (!std::strcmp(name, "host_bands")) {
         if (value < 0 || value > RT_MAX_BANDS) return fail(RT_B200_ERR_ARG, "host_bands must be 0..%d", RT_MAX_BANDS);

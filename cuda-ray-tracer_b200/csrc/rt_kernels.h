@@ -16,6 +16,7 @@ struct WaveLaunch {
     float sphere_r2_max;                // max r^2 over sphere-class objects (filter error bound)
     int shadow_cache;                   // 1 / 0 / -1 = automatic (on when the scene has >= 8 objects)
     int variant;                        // 0 = automatic; 1/2/3 = 256-thread CTAs, min 1/2/3 per SM; 5 = 512-thread CTA
+    int cubic_filter;                   // 1 = FP32 filter in front of the exact cubic test (rt_cubic_filter.cuh)
 };
 cudaError_t launch_render_wave(const SceneView &scene, const FrameParams &frame, const WaveLaunch &wl, cudaStream_t stream);
 

@@ -50,7 +50,7 @@ struct SceneView {
 // Work counters, one 64-bit slot each; order matches rt_b200_counters in include/rt_b200.h.
 enum Counter {
     CNT_PRIMARY, CNT_REFLECTION, CNT_SHADOW, CNT_HITS, CNT_LIT,
-    CNT_T_PLANE, CNT_T_SPHERE, CNT_T_QUADRIC, CNT_T_CUBIC, CNT_CONFIRM, CNT_COUNT
+    CNT_T_PLANE, CNT_T_SPHERE, CNT_T_QUADRIC, CNT_T_CUBIC, CNT_CONFIRM, CNT_CUBIC_EXACT, CNT_COUNT
 };
 
 struct FrameParams {

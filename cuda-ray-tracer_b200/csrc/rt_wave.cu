@@ -26,7 +26,7 @@ namespace {
 
 // ---- phase A: nearest hit (update-cpu.cpp:48-56) ---------------------------------------------------------
 __device__ __forceinline__ Hit nearest_hit_wave(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg,
-                                                const d3 &o, const d3 &d, Tally &tl)
+                                                const d3 &o, const d3 &d, bool primary, bool filter, Tally &tl)
 {
     Hit h;
     h.t = CUDART_INF;
@@ -64,8 +64,25 @@ __device__ __forceinline__ Hit nearest_hit_wave(const SceneView &g, const SceneS
     }
     for (int i = 0; i < g.n_quadric; i++, slot++)
         consider_lazy(h, intersect_quadric(s.quadric + 10 * i, o, d), slot, g.orig_index);
-    for (int i = 0; i < g.n_cubic; i++, slot++)
-        consider_lazy(h, intersect_cubic_masked(s.cubic + 20 * i, s.cubic_mask[i], o, d), slot, g.orig_index);
+    if (g.n_cubic > 0) {
+        // FP32 filter first: a proven miss needs no FP64 expansion and no cbrt/acos/cos (rt_cubic_filter.cuh).
+        // Primary rays share the origin, so their origin half comes from the per-CTA cache.
+        const float ofx = (float) o.x, ofy = (float) o.y, ofz = (float) o.z;
+        const float dfx = (float) d.x, dfy = (float) d.y, dfz = (float) d.z;
+        unsigned exact = 0;
+        for (int i = 0; i < g.n_cubic; i++, slot++) {
+            if (cfg.use_cubic_filter && filter) {
+                const float *kf = s.cubic_f + RT_CF_FLOATS * i;
+                const CubicD cd = make_cubic_d(kf, dfx, dfy, dfz);
+                const int v = primary ? cubic_verdict_od(s.cam_o[i], cd, (float) RT_MAX_T, false)
+                                      : cubic_verdict_od(make_cubic_o(kf, ofx, ofy, ofz), cd, (float) RT_MAX_T, false);
+                if (v == CV_MISS) continue;
+            }
+            exact++;
+            consider_lazy(h, intersect_cubic_masked(s.cubic + 20 * i, s.cubic_mask[i], o, d), slot, g.orig_index);
+        }
+        tl.n[CNT_CUBIC_EXACT] += exact;
+    }
     if (h.slot >= 0) h.orig = __ldg(&g.orig_index[h.slot]);
     tl.n[CNT_T_PLANE] += g.n_plane;
     tl.n[CNT_T_SPHERE] += g.n_sphere;
@@ -95,6 +112,7 @@ __device__ __forceinline__ double intersect_slot(const SceneView &g, const Scene
     }
     slot -= g.n_quadric;
     tl.n[CNT_T_CUBIC]++;
+    tl.n[CNT_CUBIC_EXACT]++;
     return intersect_cubic_masked(s.cubic + 20 * slot, s.cubic_mask[slot], o, d);
 }
 
@@ -137,12 +155,34 @@ __device__ __forceinline__ int occluder_spheres(const SceneView &g, const SceneS
     return found;
 }
 
-__device__ __forceinline__ int occluder_cubics(const SceneView &g, const SceneSmem &s, const d3 &o, const d3 &d,
-                                               double max_t, Tally &tl)
+// hit_slot / light: wave slot of the hit this shadow ray starts from and index of the light it goes to, the keys of
+// the filter caches (SceneSmem::hit_o, light_d) that exist when the scene has exactly one cubic.
+__device__ __forceinline__ int occluder_cubics(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg, const d3 &o,
+                                               const d3 &d, double max_t, int hit_slot, int light, Tally &tl)
 {
     const int base = g.n_plane + g.n_sphere + g.n_quadric;
+    const float hi = (float) max_t;   // 1 or 1e6, both exact in FP32
+    const float dfx = (float) d.x, dfy = (float) d.y, dfz = (float) d.z;
+    if (cfg.use_cubic_filter && s.hit_o) {
+        tl.n[CNT_T_CUBIC]++;
+        // point light: the direction differs per hit; directional light: cached per light
+        const CubicD cd = (hi == 1.0f) ? make_cubic_d(s.cubic_f, dfx, dfy, dfz) : s.light_d[light];
+        const int v = cubic_verdict_od(s.hit_o[hit_slot], cd, hi, true);
+        if (v == CV_MISS) return -1;
+        if (v == CV_HIT) return base;
+        tl.n[CNT_CUBIC_EXACT]++;
+        return blocks(intersect_cubic_masked(s.cubic, s.cubic_mask[0], o, d), max_t) ? base : -1;
+    }
+    const float ofx = (float) o.x, ofy = (float) o.y, ofz = (float) o.z;
     for (int i = 0; i < g.n_cubic; i++) {
         tl.n[CNT_T_CUBIC]++;
+        if (cfg.use_cubic_filter) {
+            const float *kf = s.cubic_f + RT_CF_FLOATS * i;
+            const int v = cubic_verdict_od(make_cubic_o(kf, ofx, ofy, ofz), make_cubic_d(kf, dfx, dfy, dfz), hi, true);
+            if (v == CV_MISS) continue;
+            if (v == CV_HIT) return base + i;
+        }
+        tl.n[CNT_CUBIC_EXACT]++;
         if (blocks(intersect_cubic_masked(s.cubic + 20 * i, s.cubic_mask[i], o, d), max_t)) return base + i;
     }
     return -1;
@@ -150,7 +190,7 @@ __device__ __forceinline__ int occluder_cubics(const SceneView &g, const SceneSm
 
 template <bool SEGMENT01>
 __device__ __forceinline__ int occluder_wave(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg, WaveCtl &ctl,
-                                             const d3 &o, const d3 &d, double max_t, Tally &tl)
+                                             const d3 &o, const d3 &d, double max_t, int hit_slot, int light, Tally &tl)
 {
     for (int i = 0; i < g.n_plane; i++) {
         tl.n[CNT_T_PLANE]++;
@@ -161,17 +201,17 @@ __device__ __forceinline__ int occluder_wave(const SceneView &g, const SceneSmem
         tl.n[CNT_T_QUADRIC]++;
         if (blocks(intersect_quadric(s.quadric + 10 * i, o, d), max_t)) return quad_base + i;
     }
-    if (g.n_sphere == 0) return g.n_cubic ? occluder_cubics(g, s, o, d, max_t, tl) : -1;
+    if (g.n_sphere == 0) return g.n_cubic ? occluder_cubics(g, s, cfg, o, d, max_t, hit_slot, light, tl) : -1;
     if (g.n_cubic == 0) return occluder_spheres<SEGMENT01>(g, s, cfg, o, d, max_t, tl);
     // relative cost of a full pass: ~4 issue slots x 4 per sphere filter, ~600 per exact cubic test
     const volatile int *found = ctl.occ_found;
     const bool cubic_first = (long long) found[1] * (16LL * g.n_sphere) > (long long) found[0] * (600LL * g.n_cubic);
-    int by = cubic_first ? occluder_cubics(g, s, o, d, max_t, tl) : occluder_spheres<SEGMENT01>(g, s, cfg, o, d, max_t, tl);
+    int by = cubic_first ? occluder_cubics(g, s, cfg, o, d, max_t, hit_slot, light, tl) : occluder_spheres<SEGMENT01>(g, s, cfg, o, d, max_t, tl);
     if (by >= 0) {
         atomicAdd(&ctl.occ_found[cubic_first ? 1 : 0], 1);
         return by;
     }
-    by = cubic_first ? occluder_spheres<SEGMENT01>(g, s, cfg, o, d, max_t, tl) : occluder_cubics(g, s, o, d, max_t, tl);
+    by = cubic_first ? occluder_spheres<SEGMENT01>(g, s, cfg, o, d, max_t, tl) : occluder_cubics(g, s, cfg, o, d, max_t, hit_slot, light, tl);
     if (by >= 0) atomicAdd(&ctl.occ_found[cubic_first ? 0 : 1], 1);
     return by;
 }

@@ -3,6 +3,7 @@
 #define RT_WAVE_CUH
 
 #include "rt_cubic.cuh"
+#include "rt_cubic_filter.cuh"
 #include "rt_filter.cuh"
 #include "rt_trace.cuh"
 
@@ -18,6 +19,10 @@ struct SceneSmem {
     const double *quadric;
     const double *cubic;
     const unsigned *cubic_mask;
+    const float *cubic_f;        // [n_cubic][RT_CF_FLOATS]: FP32 tables of the cubic filter (rt_cubic_filter.cuh)
+    const CubicO *cam_o;         // [n_cubic]: origin half of the filter for the camera origin (all primary rays)
+    const CubicD *light_d;       // [n_lights]: direction half per directional light   } only when the scene has
+    CubicO *hit_o;               // [W]: origin half per hit of the current wave        } exactly one cubic, else null
     const LightDev *lights;
 };
 
@@ -48,12 +53,15 @@ struct WaveCtl {
     int warp_base[MAX_WARPS];
     int shadow_cache[LIGHT_CHUNK];
     int occ_found[2];            // occluders found so far by [0] the sphere pass, [1] the cubic pass
+    int prim_rays, prim_hits;    // recent primary rays / hits of this CTA (decayed): the cubic filter runs on primary
+    int prim_filter;             // rays only while enough of them miss for a proven miss to pay for the filter
 };
 
 struct WaveConfig {
     int tiles_x, tiles_y;        // 32 x (W/32) pixel tiles over [local_rows][width]
     int spheres_in_smem;
     int use_shadow_cache;
+    int use_cubic_filter;
     unsigned long long *tile_counter;
     const unsigned *cubic_mask;  // global copy
     float sphere_r2_max;
@@ -70,7 +78,17 @@ __host__ __device__ inline size_t wave_scene_smem(const SceneView &sc, bool sphe
 {
     return align16(sizeof(double4) * sc.n_plane) + (spheres ? align16(sizeof(float4) * sc.n_sphere) : 0) +
            align16(sizeof(double) * 10 * sc.n_quadric) + align16(sizeof(double) * 20 * sc.n_cubic) +
-           align16(sizeof(unsigned) * sc.n_cubic) + align16(sizeof(LightDev) * sc.n_lights);
+           align16(sizeof(unsigned) * sc.n_cubic) + align16(sizeof(float) * RT_CF_FLOATS * sc.n_cubic) +
+           align16(sizeof(LightDev) * sc.n_lights);
+}
+
+// filter caches behind the scene arrays: per cubic the camera-origin half; for single-cubic scenes also the per-light
+// direction halves and one origin half per wave slot (the shadow origin of that slot's hit)
+__host__ __device__ inline size_t wave_cubic_smem(const SceneView &sc, int wave)
+{
+    size_t n = align16(sizeof(CubicO) * sc.n_cubic);
+    if (sc.n_cubic == 1) n += align16(sizeof(CubicD) * sc.n_lights) + align16(sizeof(CubicO) * wave);
+    return n;
 }
 
 } // namespace rt

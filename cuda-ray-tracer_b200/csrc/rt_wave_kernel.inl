@@ -69,14 +69,40 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         sp += align16(sizeof(unsigned) * g.n_cubic);
         for (int i = tid; i < g.n_cubic; i += WAVE) cm[i] = cfg.cubic_mask[i];
         s.cubic_mask = cm;
+        float *cf = reinterpret_cast<float *>(sp);
+        sp += align16(sizeof(float) * RT_CF_FLOATS * g.n_cubic);
+        for (int i = tid; i < g.n_cubic; i += WAVE) make_cubicf(g.cubic + 20 * i, cf + RT_CF_FLOATS * i);
+        s.cubic_f = cf;
         LightDev *lt = reinterpret_cast<LightDev *>(sp);
         for (int i = tid; i < g.n_lights; i += WAVE) lt[i] = g.lights[i];
         s.lights = lt;
         if (tid == 0) {
             ctl.pool_count = 0;
             ctl.occ_found[0] = ctl.occ_found[1] = 0;
+            ctl.prim_rays = ctl.prim_hits = 0;
+            ctl.prim_filter = 1;
         }
         if (tid < LIGHT_CHUNK) ctl.shadow_cache[tid] = -1;
+        __syncthreads();
+        // cubic filter caches (rt_cubic_filter.cuh): what depends only on the camera origin / on a directional light
+        sp += align16(sizeof(LightDev) * g.n_lights);
+        CubicO *co = reinterpret_cast<CubicO *>(sp);
+        sp += align16(sizeof(CubicO) * g.n_cubic);
+        for (int i = tid; i < g.n_cubic; i += WAVE)
+            co[i] = make_cubic_o(s.cubic_f + RT_CF_FLOATS * i, (float) f.origin[0], (float) f.origin[1], (float) f.origin[2]);
+        s.cam_o = co;
+        s.light_d = nullptr;
+        s.hit_o = nullptr;
+        if (g.n_cubic == 1) {
+            CubicD *ld = reinterpret_cast<CubicD *>(sp);
+            sp += align16(sizeof(CubicD) * g.n_lights);
+            for (int j = tid; j < g.n_lights; j += WAVE) {
+                const LightDev l = s.lights[j];      // directional: shadow_dir() is the float-rounded light vector
+                ld[j] = make_cubic_d(s.cubic_f, (float) l.px, (float) l.py, (float) l.pz);
+            }
+            s.light_d = ld;
+            s.hit_o = reinterpret_cast<CubicO *>(sp);
+        }
     }
     __syncthreads();
 
@@ -101,6 +127,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         }
         __syncthreads();
         int tile = ctl.tile;
+        const bool prim_filter = ctl.prim_filter != 0;
         if (tile >= n_tiles) {
             tiles_left = false;
             tile = -1;
@@ -153,13 +180,16 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         // ---- phase A + B: nearest hit, hit record, compact hit list ---------------------------------------
         int obj = -1;
         if (active) {
-            Hit h = nearest_hit_wave(g, s, cfg, o, d, tl);
+            Hit h = nearest_hit_wave(g, s, cfg, o, d, primary, !primary || prim_filter, tl);
             if (h.slot >= 0) {
                 obj = h.orig;
                 const d3 p = d3{o.x + h.t * d.x, o.y + h.t * d.y, o.z + h.t * d.z};
                 const d3 n = surface_normal(g.coef_full + 20 * obj, p);
                 wh.px[tid] = p.x; wh.py[tid] = p.y; wh.pz[tid] = p.z;
                 wh.nx[tid] = n.x; wh.ny[tid] = n.y; wh.nz[tid] = n.z;
+                if (s.hit_o && cfg.use_cubic_filter)   // origin half of the filter, shared by this hit's shadow rays
+                    s.hit_o[tid] = make_cubic_o(s.cubic_f, (float) (p.x + RT_SHADOW_BIAS * n.x), (float) (p.y + RT_SHADOW_BIAS * n.y),
+                                                (float) (p.z + RT_SHADOW_BIAS * n.z));
                 if (COUNT) tl.n[CNT_HITS]++;
             }
         }
@@ -182,6 +212,14 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         }
         __syncthreads();
         const int n_hits = ctl.n_hits;
+        if (primary && tid == 0 && g.n_cubic > 0) {
+            // the filter costs about a third of an exact test and saves one only for rays that miss
+            int rays = ctl.prim_rays + WAVE, hits = ctl.prim_hits + n_hits;
+            if (rays >= 16 * WAVE) { rays >>= 1; hits >>= 1; }
+            ctl.prim_rays = rays;
+            ctl.prim_hits = hits;
+            ctl.prim_filter = (5 * hits < 3 * rays) ? 1 : 0;     // on while fewer than 60 % of the primary rays hit
+        }
 
         // ---- phases C + D per chunk of 32 lights ---------------------------------------------------------------
         float acc_r = 0.f, acc_g = 0.f, acc_b = 0.f;
@@ -192,26 +230,46 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
             if (hit) wh.occluded[tid] = 0u;
             __syncthreads();
             // C: task = (light j, hit i), light-major
+            const unsigned inv_hits = n_hits > 1 ? (unsigned) ((0x100000000ULL + n_hits - 1) / (unsigned) n_hits) : 0u;   // ceil(2^32 / n)
+            const bool lone_cubic = s.hit_o != nullptr && cfg.use_cubic_filter && g.n_objects == 1;
             for (int task = tid; task < n_hits * lc; task += WAVE) {
-                const int j = task / n_hits;
+                const int j = n_hits > 1 ? (int) __umulhi((unsigned) task, inv_hits) : task;   // task / n_hits (task * n_hits < 2^32)
                 const int k = wh.hitlist[task - j * n_hits];
                 const LightDev l = s.lights[l0 + j];
                 const d3 p = d3{wh.px[k], wh.py[k], wh.pz[k]};
-                const d3 n = d3{wh.nx[k], wh.ny[k], wh.nz[k]};
-                const d3 so = d3{p.x + RT_SHADOW_BIAS * n.x, p.y + RT_SHADOW_BIAS * n.y, p.z + RT_SHADOW_BIAS * n.z};
-                double max_t;
-                const d3 sd = shadow_dir(l, p, max_t);
                 if (COUNT) tl.n[CNT_SHADOW]++;
                 bool occ = false;
-                if (cfg.use_shadow_cache) {
-                    const int cs = ctl.shadow_cache[j];
-                    if (cs >= 0) occ = blocks(intersect_slot(g, s, cs, so, sd, tl), max_t);
+                int verdict = CV_UNKNOWN;
+                if (lone_cubic) {
+                    // the only object is one cubic: the cached filter halves decide most shadow rays without
+                    // touching FP64 (rt_cubic_filter.cuh); the exact path below runs for the undecided ones
+                    if (COUNT) tl.n[CNT_T_CUBIC]++;
+                    const CubicD cd = l.is_spherical ? make_cubic_d(s.cubic_f, (float) (l.px - p.x), (float) (l.py - p.y), (float) (l.pz - p.z))
+                                                     : s.light_d[l0 + j];
+                    verdict = cubic_verdict_od(s.hit_o[k], cd, l.is_spherical ? 1.0f : (float) RT_MAX_T, true);
+                    occ = verdict == CV_HIT;
                 }
-                if (!occ) {
-                    const int by = l.is_spherical ? occluder_wave<true>(g, s, cfg, ctl, so, sd, max_t, tl)
-                                                  : occluder_wave<false>(g, s, cfg, ctl, so, sd, max_t, tl);
-                    occ = by >= 0;
-                    if (occ && cfg.use_shadow_cache) ctl.shadow_cache[j] = by;   // benign race: any occluder will do
+                if (verdict == CV_UNKNOWN) {
+                    const d3 n = d3{wh.nx[k], wh.ny[k], wh.nz[k]};
+                    const d3 so = d3{p.x + RT_SHADOW_BIAS * n.x, p.y + RT_SHADOW_BIAS * n.y, p.z + RT_SHADOW_BIAS * n.z};
+                    double max_t;
+                    const d3 sd = shadow_dir(l, p, max_t);
+                    if (lone_cubic) {
+                        if (COUNT) tl.n[CNT_CUBIC_EXACT]++;
+                        occ = blocks(intersect_cubic_masked(s.cubic, s.cubic_mask[0], so, sd), max_t);
+                    }
+                    else {
+                        if (cfg.use_shadow_cache) {
+                            const int cs = ctl.shadow_cache[j];
+                            if (cs >= 0) occ = blocks(intersect_slot(g, s, cs, so, sd, tl), max_t);
+                        }
+                        if (!occ) {
+                            const int by = l.is_spherical ? occluder_wave<true>(g, s, cfg, ctl, so, sd, max_t, k, l0 + j, tl)
+                                                          : occluder_wave<false>(g, s, cfg, ctl, so, sd, max_t, k, l0 + j, tl);
+                            occ = by >= 0;
+                            if (occ && cfg.use_shadow_cache) ctl.shadow_cache[j] = by;   // benign race: any occluder will do
+                        }
+                    }
                 }
                 if (occ) atomicOr(&wh.occluded[k], 1u << j);
             }
@@ -302,7 +360,7 @@ cudaError_t launch_wave_variant(const SceneView &scene, const FrameParams &frame
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    const size_t smem = wave_fixed_smem<W>() + scene_smem;
+    const size_t smem = wave_fixed_smem<W>() + scene_smem + wave_cubic_smem(scene, W);
     cfg.tiles_x = (frame.width + 31) / 32;
     cfg.tiles_y = (frame.rows + W / 32 - 1) / (W / 32);
     int per_sm = 1;
@@ -338,14 +396,15 @@ cudaError_t launch_render_wave(const SceneView &scene, const FrameParams &frame,
     cfg.cubic_mask = wl.cubic_mask;
     cfg.sphere_r2_max = wl.sphere_r2_max;
     cfg.use_shadow_cache = wl.shadow_cache >= 0 ? wl.shadow_cache : (scene.n_objects >= 8 ? 1 : 0);
+    cfg.use_cubic_filter = wl.cubic_filter;
     cfg.spheres_in_smem = 1;
     size_t scene_smem = wave_scene_smem(scene, true);
-    if (wave_fixed_smem<512>() + scene_smem > (size_t) max_smem) {
+    if (wave_fixed_smem<512>() + scene_smem + wave_cubic_smem(scene, 512) > (size_t) max_smem) {
         cfg.spheres_in_smem = 0;
         scene_smem = wave_scene_smem(scene, false);
-        if (wave_fixed_smem<256>() + scene_smem > (size_t) max_smem) return cudaErrorInvalidConfiguration;
+        if (wave_fixed_smem<256>() + scene_smem + wave_cubic_smem(scene, 256) > (size_t) max_smem) return cudaErrorInvalidConfiguration;
     }
-    const size_t cta256 = wave_fixed_smem<256>() + scene_smem + 1024;   // + per-CTA reservation
+    const size_t cta256 = wave_fixed_smem<256>() + scene_smem + wave_cubic_smem(scene, 256) + 1024;   // + per-CTA reservation
     int variant = wl.variant;
     if (variant <= 0) variant = (3 * cta256 <= (size_t) sm_smem) ? 3 : 5;
     switch (variant) {

@@ -54,6 +54,8 @@ typedef struct {
     uint64_t tests_quadric;
     uint64_t tests_cubic;
     uint64_t fp64_confirms;   /* sphere tests that fell through the FP32 filter to the exact FP64 test */
+    uint64_t cubic_exact;     /* cubic-class tests that needed the exact FP64 expansion + solve (the others were
+                               * decided by the FP32 filter); kernel 1 only, kernels 0 and 2 test exactly and leave 0 */
 } rt_b200_counters;
 
 /* == init_update(texture, scene), update.h:6.
@@ -140,7 +142,8 @@ int rt_b200_get_counters(rt_b200_ctx *ctx, rt_b200_counters *out);
  *                           scene exceeds its parameter block)
  *          "host_bands" row bands of rt_b200_update_to_host (0 = automatic, about 4 MB each)
  *          "strip_rows" image rows per strip of the multi-GPU interleave (default 8)
- *          "count"      1 = maintain rt_b200_counters (default), 0 = skip them                       */
+ *          "count"      1 = maintain rt_b200_counters (default), 0 = skip them
+ *          "cubic_filter" 1 = FP32 filter in front of the exact cubic test in kernel 1 (default), 0 = off    */
 int rt_b200_set_option(rt_b200_ctx *ctx, const char *name, int64_t value);
 
 /* Split timing of the last update, milliseconds: [0] render kernels, [1] gather (all-gather + unpack). */

@@ -33,4 +33,7 @@ for name, sc in todo:
                 base = img
             row["v%d" % v] = round(ms, 4)
             row["same%d" % v] = bool(np.array_equal(img, base))
+        c = r.counters()
+        row["cubic_tests"] = c["tests_cubic"]
+        row["cubic_exact"] = c["cubic_exact"]
     print(json.dumps(row), flush=True)
