@@ -25,6 +25,8 @@ namespace rt {
 namespace {
 
 // ---- phase A: nearest hit (update-cpu.cpp:48-56) ---------------------------------------------------------
+// CUBIC = false compiles the cubic class out (scenes without cubics run a leaner kernel).
+template <bool CUBIC>
 __device__ __forceinline__ Hit nearest_hit_wave(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg,
                                                 const d3 &o, const d3 &d, bool primary, bool filter, Tally &tl)
 {
@@ -64,7 +66,7 @@ __device__ __forceinline__ Hit nearest_hit_wave(const SceneView &g, const SceneS
     }
     for (int i = 0; i < g.n_quadric; i++, slot++)
         consider_lazy(h, intersect_quadric(s.quadric + 10 * i, o, d), slot, g.orig_index);
-    if (g.n_cubic > 0) {
+    if (CUBIC && g.n_cubic > 0) {
         // FP32 filter first: a proven miss needs no FP64 expansion and no cbrt/acos/cos (rt_cubic_filter.cuh).
         // Primary rays share the origin, so their origin half comes from the per-CTA cache.
         const float ofx = (float) o.x, ofy = (float) o.y, ofz = (float) o.z;
@@ -87,11 +89,12 @@ __device__ __forceinline__ Hit nearest_hit_wave(const SceneView &g, const SceneS
     tl.n[CNT_T_PLANE] += g.n_plane;
     tl.n[CNT_T_SPHERE] += g.n_sphere;
     tl.n[CNT_T_QUADRIC] += g.n_quadric;
-    tl.n[CNT_T_CUBIC] += g.n_cubic;
+    if (CUBIC) tl.n[CNT_T_CUBIC] += g.n_cubic;
     return h;
 }
 
 // exact test of one class-sorted slot (shadow cache probe)
+template <bool CUBIC>
 __device__ __forceinline__ double intersect_slot(const SceneView &g, const SceneSmem &s, int slot, const d3 &o,
                                                  const d3 &d, Tally &tl)
 {
@@ -111,6 +114,7 @@ __device__ __forceinline__ double intersect_slot(const SceneView &g, const Scene
         return intersect_quadric(s.quadric + 10 * slot, o, d);
     }
     slot -= g.n_quadric;
+    if (!CUBIC) return -1.0;
     tl.n[CNT_T_CUBIC]++;
     tl.n[CNT_CUBIC_EXACT]++;
     return intersect_cubic_masked(s.cubic + 20 * slot, s.cubic_mask[slot], o, d);
@@ -188,7 +192,7 @@ __device__ __forceinline__ int occluder_cubics(const SceneView &g, const SceneSm
     return -1;
 }
 
-template <bool SEGMENT01>
+template <bool SEGMENT01, bool CUBIC>
 __device__ __forceinline__ int occluder_wave(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg, WaveCtl &ctl,
                                              const d3 &o, const d3 &d, double max_t, int hit_slot, int light, Tally &tl)
 {
@@ -201,8 +205,8 @@ __device__ __forceinline__ int occluder_wave(const SceneView &g, const SceneSmem
         tl.n[CNT_T_QUADRIC]++;
         if (blocks(intersect_quadric(s.quadric + 10 * i, o, d), max_t)) return quad_base + i;
     }
-    if (g.n_sphere == 0) return g.n_cubic ? occluder_cubics(g, s, cfg, o, d, max_t, hit_slot, light, tl) : -1;
-    if (g.n_cubic == 0) return occluder_spheres<SEGMENT01>(g, s, cfg, o, d, max_t, tl);
+    if (g.n_sphere == 0) return (CUBIC && g.n_cubic) ? occluder_cubics(g, s, cfg, o, d, max_t, hit_slot, light, tl) : -1;
+    if (!CUBIC || g.n_cubic == 0) return occluder_spheres<SEGMENT01>(g, s, cfg, o, d, max_t, tl);
     // relative cost of a full pass: ~4 issue slots x 4 per sphere filter, ~600 per exact cubic test
     const volatile int *found = ctl.occ_found;
     const bool cubic_first = (long long) found[1] * (16LL * g.n_sphere) > (long long) found[0] * (600LL * g.n_cubic);

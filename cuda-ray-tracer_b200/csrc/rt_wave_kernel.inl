@@ -26,7 +26,7 @@ __device__ __forceinline__ float blend(float out, float ratio, float c) { return
 
 } // namespace
 
-template <int W, int MINB, bool COUNT>
+template <int W, int MINB, bool COUNT, bool CUBIC>
 __global__ void __launch_bounds__(W, MINB)
 render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ FrameParams f,
                    const __grid_constant__ WaveConfig cfg)
@@ -93,7 +93,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         s.cam_o = co;
         s.light_d = nullptr;
         s.hit_o = nullptr;
-        if (g.n_cubic == 1) {
+        if (CUBIC && g.n_cubic == 1) {
             CubicD *ld = reinterpret_cast<CubicD *>(sp);
             sp += align16(sizeof(CubicD) * g.n_lights);
             for (int j = tid; j < g.n_lights; j += WAVE) {
@@ -180,14 +180,14 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         // ---- phase A + B: nearest hit, hit record, compact hit list ---------------------------------------
         int obj = -1;
         if (active) {
-            Hit h = nearest_hit_wave(g, s, cfg, o, d, primary, !primary || prim_filter, tl);
+            Hit h = nearest_hit_wave<CUBIC>(g, s, cfg, o, d, primary, !primary || prim_filter, tl);
             if (h.slot >= 0) {
                 obj = h.orig;
                 const d3 p = d3{o.x + h.t * d.x, o.y + h.t * d.y, o.z + h.t * d.z};
                 const d3 n = surface_normal(g.coef_full + 20 * obj, p);
                 wh.px[tid] = p.x; wh.py[tid] = p.y; wh.pz[tid] = p.z;
                 wh.nx[tid] = n.x; wh.ny[tid] = n.y; wh.nz[tid] = n.z;
-                if (s.hit_o && cfg.use_cubic_filter)   // origin half of the filter, shared by this hit's shadow rays
+                if (CUBIC && s.hit_o && cfg.use_cubic_filter)   // origin half of the filter, shared by this hit's shadow rays
                     s.hit_o[tid] = make_cubic_o(s.cubic_f, (float) (p.x + RT_SHADOW_BIAS * n.x), (float) (p.y + RT_SHADOW_BIAS * n.y),
                                                 (float) (p.z + RT_SHADOW_BIAS * n.z));
                 if (COUNT) tl.n[CNT_HITS]++;
@@ -212,7 +212,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         }
         __syncthreads();
         const int n_hits = ctl.n_hits;
-        if (primary && tid == 0 && g.n_cubic > 0) {
+        if (CUBIC && primary && tid == 0 && g.n_cubic > 0) {
             // the filter costs about a third of an exact test and saves one only for rays that miss
             int rays = ctl.prim_rays + WAVE, hits = ctl.prim_hits + n_hits;
             if (rays >= 16 * WAVE) { rays >>= 1; hits >>= 1; }
@@ -231,7 +231,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
             __syncthreads();
             // C: task = (light j, hit i), light-major
             const unsigned inv_hits = n_hits > 1 ? (unsigned) ((0x100000000ULL + n_hits - 1) / (unsigned) n_hits) : 0u;   // ceil(2^32 / n)
-            const bool lone_cubic = s.hit_o != nullptr && cfg.use_cubic_filter && g.n_objects == 1;
+            const bool lone_cubic = CUBIC && s.hit_o != nullptr && cfg.use_cubic_filter && g.n_objects == 1;
             for (int task = tid; task < n_hits * lc; task += WAVE) {
                 const int j = n_hits > 1 ? (int) __umulhi((unsigned) task, inv_hits) : task;   // task / n_hits (task * n_hits < 2^32)
                 const int k = wh.hitlist[task - j * n_hits];
@@ -261,11 +261,11 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
                     else {
                         if (cfg.use_shadow_cache) {
                             const int cs = ctl.shadow_cache[j];
-                            if (cs >= 0) occ = blocks(intersect_slot(g, s, cs, so, sd, tl), max_t);
+                            if (cs >= 0) occ = blocks(intersect_slot<CUBIC>(g, s, cs, so, sd, tl), max_t);
                         }
                         if (!occ) {
-                            const int by = l.is_spherical ? occluder_wave<true>(g, s, cfg, ctl, so, sd, max_t, k, l0 + j, tl)
-                                                          : occluder_wave<false>(g, s, cfg, ctl, so, sd, max_t, k, l0 + j, tl);
+                            const int by = l.is_spherical ? occluder_wave<true, CUBIC>(g, s, cfg, ctl, so, sd, max_t, k, l0 + j, tl)
+                                                          : occluder_wave<false, CUBIC>(g, s, cfg, ctl, so, sd, max_t, k, l0 + j, tl);
                             occ = by >= 0;
                             if (occ && cfg.use_shadow_cache) ctl.shadow_cache[j] = by;   // benign race: any occluder will do
                         }
@@ -351,12 +351,15 @@ cudaError_t launch_wave_variant(const SceneView &scene, const FrameParams &frame
                                 int n_sm, int max_smem, cudaStream_t stream)
 {
     static bool attr_set = false;
-    auto kern = frame.counters ? render_wave_kernel<W, MINB, true> : render_wave_kernel<W, MINB, false>;
+    const bool cubic = scene.n_cubic > 0;
+    auto kern = cubic ? (frame.counters ? render_wave_kernel<W, MINB, true, true> : render_wave_kernel<W, MINB, false, true>)
+                      : (frame.counters ? render_wave_kernel<W, MINB, true, false> : render_wave_kernel<W, MINB, false, false>);
     cudaError_t e;
     if (!attr_set) {
-        e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
