@@ -269,11 +269,18 @@ def run_b200(args):
                     r.gather_into(host_frame.data_ptr(), nbytes)
 
     # ---- census (untimed): rays and tests of one step, with the kernel's counters on -----------------
-    local_counts = {}
+    # The metric counts the rays the REFERENCE casts for these frames: census with culling off.  The
+    # timed runs use the product default (culling on): shadow rays that provably add 0 to the pixel are not traced;
+    # that smaller number is reported beside it as rays_traced_per_step.
+    local_counts, traced_counts = {}, {}
     for label, _, r in renderers:
         r.set_option("count", 1)
+        r.set_option("cull_backfacing", 0)
         r.update(m)
         local_counts[label] = r.counters()
+        r.set_option("cull_backfacing", 1 if args.cull else 0)
+        r.update(m)
+        traced_counts[label] = r.counters()
         r.set_option("count", 0)        # counters are instrumentation, not part of the frame: off while timing
 
     # ---- device-resident timing ------------------------------------------------------------------
@@ -316,14 +323,15 @@ def run_b200(args):
     times = torch.tensor([dt, dt_e2e, ev_ms / 1e3], dtype=torch.float64, device="cuda")
     kern = torch.tensor([[per_scene[label]["render_ms"], per_scene[label]["gather_ms"]] for label, _, _ in renderers],
                         dtype=torch.float64, device="cuda")
-    nl = torch.tensor([launches], dtype=torch.int64, device="cuda")
+    nl = torch.tensor([launches, sum(c["primary_rays"] + c["reflection_rays"] + c["shadow_rays"]
+                                     for c in traced_counts.values())], dtype=torch.int64, device="cuda")
     if world > 1:
         dist.all_reduce(mat, op=dist.ReduceOp.SUM)
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
         dist.all_reduce(kern, op=dist.ReduceOp.MAX)
         dist.all_reduce(nl, op=dist.ReduceOp.SUM)
     mat, times, kern = mat.cpu().numpy(), times.cpu().numpy(), kern.cpu().numpy() / args.steps
-    launches = int(nl.item())
+    launches, rays_traced = int(nl[0].item()), int(nl[1].item())
 
     if rank == 0:
         peaks = load_peaks()
@@ -359,7 +367,9 @@ def run_b200(args):
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "ms_per_step_wall": ms_wall, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": args.workload, "description": desc, "frames_per_step": len(renderers),
-                       "rays_per_step": rays_step, "kernel": args.kernel,
+                       "rays_per_step": rays_step, "rays_traced_per_step": rays_traced,
+                       "ray_count": "rays_per_step = rays the reference casts (metric); rays_traced_per_step = rays this kernel "
+                                    "traces: shadow rays towards lights with Lambert factor 0 at the hit add exactly 0 and are skipped", "kernel": args.kernel,
                        "parallelism": "strips{}x{}rows,{}".format(world, args.strip_rows, "p2p-store+flags" if fused else
                                                                   "nccl-allgather") if world > 1 else "1gpu",
                        "timing": "CUDA events on the render stream per frame, summed; max over ranks",
@@ -437,6 +447,7 @@ def main():
     ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"], help="multi-GPU frame assembly")
     ap.add_argument("--e2e", default="shared", choices=["shared", "gather"], help="multi-GPU end-to-end leg: every rank "
                     "copies its strips into one shared host frame, or rank 0 gathers on the device and copies alone")
+    ap.add_argument("--no-cull", dest="cull", action="store_false", help="trace every shadow ray the reference casts")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -190,6 +190,8 @@ struct rt_b200_ctx {
     int shadow_cache = -1;
     int wave_variant = 0;
     int cubic_filter = 1;
+    int cull_backfacing = 1;
+    bool cull_safe = true;           // every light / object colour is finite and moderate: 0 * colour is exactly 0
     bool buffers_dirty = true;
 
     int kernel_kind = 1;
@@ -325,6 +327,7 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
         std::memcpy(color, obj_bytes + RT_B200_OBJECT_BYTES * i + 164, 12);
         std::memcpy(&coef_full[20 * i], k, 160);
         material[i] = make_float4(refl, color[0], color[1], color[2]);
+        if (!(fabsf(color[0]) < 1e5f && fabsf(color[1]) < 1e5f && fabsf(color[2]) < 1e5f)) c->cull_safe = false;
         rt::ObjClass cls = classify(k);
         orig[cls].push_back((int) i);
         switch (cls) {
@@ -372,6 +375,7 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
         std::memcpy(col, rec + 32, 12);
         ldev[j] = rt::LightDev{p[0], p[1], p[2], col[0], col[1], col[2], rec[0] != 0 ? 1 : 0};
         if (!(fabs(p[0]) < 1e9 && fabs(p[1]) < 1e9 && fabs(p[2]) < 1e9)) tables_safe = false;
+        if (!(fabsf(col[0]) < 1e15f && fabsf(col[1]) < 1e15f && fabsf(col[2]) < 1e15f)) c->cull_safe = false;
     }
 
     int rc = RT_B200_OK;
@@ -493,7 +497,7 @@ int launch_kernel(rt_b200_ctx *c, const rt::FrameParams &f)
         CUDA_TRY(rt::launch_render_queue(c->view, f, ql, c->stream));
     }
     else {   // kernel 1, and kernel 2 for scenes that exceed the queue kernel's parameter block
-        rt::WaveLaunch wl{c->d_tile_counter, c->d_cubic_mask, c->sphere_r2_max, c->shadow_cache, c->wave_variant, c->cubic_filter};
+        rt::WaveLaunch wl{c->d_tile_counter, c->d_cubic_mask, c->sphere_r2_max, c->shadow_cache, c->wave_variant, c->cubic_filter, (c->cull_backfacing && c->cull_safe) ? 1 : 0};
         CUDA_TRY(rt::launch_render_wave(c->view, f, wl, c->stream));
     }
     return RT_B200_OK;
@@ -953,6 +957,9 @@ int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
     }
     else if (!std::strcmp(name, "flag_barrier")) {
         c->flag_barrier = value != 0;
+    }
+    else if (!std::strcmp(name, "cull_backfacing")) {
+        c->cull_backfacing = value ? 1 : 0;
     }
     else if (!std::strcmp(name, "cubic_filter")) {
         c->cubic_filter = value ? 1 : 0;

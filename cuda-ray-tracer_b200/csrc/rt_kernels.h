@@ -17,6 +17,7 @@ struct WaveLaunch {
     int shadow_cache;                   // 1 / 0 / -1 = automatic (on when the scene has >= 8 objects)
     int variant;                        // 0 = automatic; 1/2/3 = 256-thread CTAs, min 1/2/3 per SM; 5 = 512-thread CTA
     int cubic_filter;                   // 1 = FP32 filter in front of the exact cubic test (rt_cubic_filter.cuh)
+    int cull_backfacing;                // 1 = no shadow ray towards a light whose Lambert factor is 0 at the hit
 };
 cudaError_t launch_render_wave(const SceneView &scene, const FrameParams &frame, const WaveLaunch &wl, cudaStream_t stream);
 

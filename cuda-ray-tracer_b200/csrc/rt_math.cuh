@@ -247,6 +247,26 @@ __device__ __forceinline__ void shade_light(const LightDev &l, const d3 &p, cons
     acc.z += obj.z / RT_PI_F * cb * lambert;
 }
 
+// The factor surface_color() multiplies a light's colour with (light_impl.h:43): max(0, (float) dot(n, dir)).  When it
+// is 0 and the colour terms are finite the light adds exactly +-0 to the pixel whether or not it is occluded, so its
+// shadow ray cannot influence the frame.  Returns true only when that is CERTAIN (false = trace the ray as usual):
+//   directional: the reference's own (float) dot(n, p) is not positive;
+//   point light: the reference normalises dir = p - P first (a positive factor), so the sign is that of
+//       u = dot(n, dir) unless u is within rounding of 0 — required: u below -1e-14 times the sum of |terms|, and
+//       |dir| > 1e-7 so that colour / (4 pi |dir|^2) stays finite.
+// The caller has checked once per scene that every light and object colour is finite and moderate (cull_safe).
+__device__ __forceinline__ bool light_cannot_contribute(const LightDev &l, const d3 &p, const d3 &n)
+{
+    if (l.is_spherical) {
+        const double dx = l.px - p.x, dy = l.py - p.y, dz = l.pz - p.z;
+        const double a = n.x * dx, b = n.y * dy, c = n.z * dz;
+        const double u = (a + b) + c;
+        return u < -1e-14 * ((fabs(a) + fabs(b)) + fabs(c)) && (fabs(dx) + fabs(dy)) + fabs(dz) > 1e-7;
+    }
+    const float cosv = (float) dot3(n, d3{l.px, l.py, l.pz});
+    return !(0.0f < cosv);
+}
+
 // light_impl.h:46-49
 __device__ __forceinline__ d3 reflect(const d3 &dir, const d3 &n)
 {

@@ -42,7 +42,7 @@ template <int W>
 struct WaveHits {
     double px[W], py[W], pz[W];
     double nx[W], ny[W], nz[W];
-    unsigned occluded[W];        // bit j: light (chunk base + j) is shadowed
+    unsigned occluded[W];        // bit j: light (chunk base + j) is shadowed (or cannot contribute)
     unsigned short hitlist[W];
 };
 
@@ -62,6 +62,7 @@ struct WaveConfig {
     int spheres_in_smem;
     int use_shadow_cache;
     int use_cubic_filter;
+    int cull_backfacing;         // skip shadow rays of lights whose Lambert factor is 0 at the hit (they add exactly 0)
     unsigned long long *tile_counter;
     const unsigned *cubic_mask;  // global copy
     float sphere_r2_max;

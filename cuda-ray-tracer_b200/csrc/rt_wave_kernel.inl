@@ -237,6 +237,11 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
                 const int k = wh.hitlist[task - j * n_hits];
                 const LightDev l = s.lights[l0 + j];
                 const d3 p = d3{wh.px[k], wh.py[k], wh.pz[k]};
+                const d3 n = d3{wh.nx[k], wh.ny[k], wh.nz[k]};
+                if (cfg.cull_backfacing && light_cannot_contribute(l, p, n)) {
+                    atomicOr(&wh.occluded[k], 1u << j);     // phase D skips it, exactly as if it were shadowed
+                    continue;
+                }
                 if (COUNT) tl.n[CNT_SHADOW]++;
                 bool occ = false;
                 int verdict = CV_UNKNOWN;
@@ -250,7 +255,6 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
                     occ = verdict == CV_HIT;
                 }
                 if (verdict == CV_UNKNOWN) {
-                    const d3 n = d3{wh.nx[k], wh.ny[k], wh.nz[k]};
                     const d3 so = d3{p.x + RT_SHADOW_BIAS * n.x, p.y + RT_SHADOW_BIAS * n.y, p.z + RT_SHADOW_BIAS * n.z};
                     double max_t;
                     const d3 sd = shadow_dir(l, p, max_t);
@@ -400,6 +404,7 @@ cudaError_t launch_render_wave(const SceneView &scene, const FrameParams &frame,
     cfg.sphere_r2_max = wl.sphere_r2_max;
     cfg.use_shadow_cache = wl.shadow_cache >= 0 ? wl.shadow_cache : (scene.n_objects >= 8 ? 1 : 0);
     cfg.use_cubic_filter = wl.cubic_filter;
+    cfg.cull_backfacing = wl.cull_backfacing;
     cfg.spheres_in_smem = 1;
     size_t scene_smem = wave_scene_smem(scene, true);
     if (wave_fixed_smem<512>() + scene_smem + wave_cubic_smem(scene, 512) > (size_t) max_smem) {

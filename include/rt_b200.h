@@ -41,7 +41,8 @@ extern "C" {
 
 typedef struct rt_b200_ctx rt_b200_ctx;
 
-/* Work actually executed by the last rt_b200_update on THIS rank (64-bit, exact).
+/* Work actually executed by the last rt_b200_update on THIS rank (64-bit, exact); with option cull_backfacing = 0
+ * this is the reference's own ray census for the frame.
  * rays = primary + reflection + shadow, the reference's ray definition. */
 typedef struct {
     uint64_t primary_rays;    /* one per pixel rendered by this rank                                   */
@@ -143,7 +144,11 @@ int rt_b200_get_counters(rt_b200_ctx *ctx, rt_b200_counters *out);
  *          "host_bands" row bands of rt_b200_update_to_host (0 = automatic, about 4 MB each)
  *          "strip_rows" image rows per strip of the multi-GPU interleave (default 8)
  *          "count"      1 = maintain rt_b200_counters (default), 0 = skip them
- *          "cubic_filter" 1 = FP32 filter in front of the exact cubic test in kernel 1 (default), 0 = off    */
+ *          "cubic_filter" 1 = FP32 filter in front of the exact cubic test in kernel 1 (default), 0 = off
+ *          "cull_backfacing" 1 (default, kernel 1): no shadow ray is traced towards a light whose Lambert factor
+ *                       max(0, n.dir) is 0 at the hit — such a light adds exactly 0 whether occluded or not, so
+ *                       frames are identical; rt_b200_counters then report the rays actually traced.  0 = trace every
+ *                       shadow ray the reference casts (the counters equal the reference's ray census)            */
 int rt_b200_set_option(rt_b200_ctx *ctx, const char *name, int64_t value);
 
 /* Split timing of the last update, milliseconds: [0] render kernels, [1] gather (all-gather + unpack). */

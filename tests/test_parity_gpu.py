@@ -40,10 +40,19 @@ def test_bundled_scenes_native_resolution(pkg, rt, oracle, scenes_dir, name, ker
         for pose in ("identity", "pose_a", "pose_b"):
             m = camera.TEST_POSES[pose]
             ref_rgb, _, cnt = port.render_rows(m, threads=os.cpu_count(), count=True)
+            # default: shadow rays towards lights whose Lambert factor is 0 at the hit are not traced (kernel 1)
+            r.set_option("cull_backfacing", 1)
             r.update(m)
-            res = assert_parity(r.gather(), oracle.quantize_rgba8(ref_rgb), "{}/{}".format(name, pose))
+            img = r.gather()
+            culled = r.counters()
+            res = assert_parity(img, oracle.quantize_rgba8(ref_rgb), "{}/{}".format(name, pose))
             assert res["exact_frac"] > 0.999, res
+            # ... which cannot change a pixel; with it off the kernel executes the reference's ray census
+            r.set_option("cull_backfacing", 0)
+            r.update(m)
+            assert np.array_equal(r.gather(), img), (name, pose, "culling changed the frame")
             c = r.counters()
+            assert culled["shadow_rays"] <= c["shadow_rays"] and culled["lit"] <= c["lit"] and culled["hits"] == c["hits"]
             if res["outliers"] == 0 and res["exact_frac"] == 1.0:
                 # same decisions everywhere -> same ray census as the reference would have executed
                 for k_gpu, k_cpu in (("primary_rays", "primary_rays"), ("reflection_rays", "reflection_rays"),
@@ -82,8 +91,9 @@ def test_full_size_properties_4k(pkg, rt, oracle, scenes_dir, name, kernel):
         r.set_option("kernel", kernel)
         r.update(m)
         a = r.gather()
+        r.set_option("cull_backfacing", 0)                                # trace every shadow ray the reference casts
         r.update(m)
-        assert np.array_equal(a, r.gather())                              # deterministic / idempotent
+        assert np.array_equal(a, r.gather())                              # deterministic; culling changes no pixel
         c = r.counters()
         assert c["primary_rays"] == 3840 * 2160 and c["shadow_rays"] == c["hits"] * len(sc.lights)
         rng = np.random.default_rng(1)
@@ -176,6 +186,7 @@ def test_update_to_host_streams_the_same_frame(pkg, rt, scenes_dir, kernel):
         host = torch.zeros(w * h * 4, dtype=torch.uint8).pin_memory()
         with rt.Renderer(sc) as r:
             r.set_option("kernel", kernel)
+            r.set_option("cull_backfacing", 0)
             r.update(camera.TEST_POSES["pose_a"])
             ref = r.gather()
             c_ref = r.counters()
