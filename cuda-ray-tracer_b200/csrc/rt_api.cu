@@ -21,6 +21,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <algorithm>
 #include <cstring>
 #include <mutex>
@@ -191,6 +192,8 @@ struct rt_b200_ctx {
     int wave_variant = 0;
     int cubic_filter = 1;
     int cull_backfacing = 1;
+    double trace[5] = {0, 0, 0, 0, 0};   // RT_B200_TRACE=1: seconds spent per stage of update_to_host (shared block)
+    unsigned trace_frames = 0;
     bool cull_safe = true;           // every light / object colour is finite and moderate: 0 * colour is exactly 0
     bool buffers_dirty = true;
 
@@ -561,7 +564,9 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
     }
     if (streamed) {
         const size_t local_bytes = sizeof(uchar4) * (size_t) c->width * c->local_rows;
-        n_bands = c->host_bands > 0 ? c->host_bands : (int) (local_bytes / (4u << 20));
+        // one GPU: ~4 MB bands; several GPUs feeding one host frame: each rank's share is small, ~1 MB bands keep
+        // its copy engine busy while it still renders
+        n_bands = c->host_bands > 0 ? c->host_bands : (int) (local_bytes / (c->world > 1 ? (1u << 20) : (4u << 20)));
         if (n_bands > RT_MAX_BANDS) n_bands = RT_MAX_BANDS;
         if (n_bands > (c->local_rows + band_unit - 1) / band_unit) n_bands = (c->local_rows + band_unit - 1) / band_unit;
         if (n_bands < 1) n_bands = 1;
@@ -572,9 +577,11 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
         host_seq = ++blk->seq;
         SharedTrailer *t = blk->trailer();
         if (c->rank == 0) __atomic_store_n(&t->go, host_seq, __ATOMIC_RELEASE);
-        else if (!host_wait_word(&t->go, host_seq, 20.0))
-            return fail(RT_B200_ERR_STATE, "rank 0 did not enter frame %u of the shared host block (timeout)", host_seq);
     }
+    static const bool tracing = std::getenv("RT_B200_TRACE") != nullptr;
+    const double t_enter = tracing ? now_seconds() : 0.0;
+    double t_go = 0.0;
+    bool go_seen = (blk == nullptr) || c->rank == 0;
 
     if (c->count) CUDA_TRY(cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long) * rt::CNT_COUNT, c->stream));
     CUDA_TRY(cudaEventRecord(c->ev_start, c->stream));
@@ -602,6 +609,15 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
                                          sizeof(uchar4) * (size_t) f.rows * c->width, cudaMemcpyDeviceToHost, c->copy_stream));
             }
             else {
+                if (!go_seen) {
+                    // the block may still hold the frame rank 0's caller is reading: wait until rank 0 has entered
+                    // this frame too (rendering is already queued, only the copies wait)
+                    const double t0 = tracing ? now_seconds() : 0.0;
+                    if (!host_wait_word(&blk->trailer()->go, host_seq, 20.0))
+                        return fail(RT_B200_ERR_STATE, "rank 0 did not enter frame %u of the shared host block (timeout)", host_seq);
+                    go_seen = true;
+                    if (tracing) t_go = now_seconds() - t0;
+                }
                 // local strip s of this rank is image strip s * world + rank: one pitched copy scatters the band's
                 // strips to their image rows; a ragged last strip goes separately; padding strips are not copied
                 const int n_strips = (c->height + c->strip_rows - 1) / c->strip_rows;
@@ -659,6 +675,7 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
         c->last_frame = nullptr;   // assembled on demand by rt_b200_gather (this rank's rows only)
     }
     CUDA_TRY(cudaEventRecord(c->ev_end, c->stream));
+    const double t_issued = tracing ? now_seconds() : 0.0;
     if (streamed) {
         CUDA_TRY(cudaEventRecord(c->ev_copy, c->copy_stream));
         CUDA_TRY(cudaStreamWaitEvent(c->stream, c->ev_copy, 0));   // keep the next frame from overwriting rows in flight
@@ -674,6 +691,7 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
     CUDA_TRY(cudaEventElapsedTime(&c->ms_gather, c->ev_render, c->ev_end));
     float total = c->ms_render + c->ms_gather;
     if (streamed) CUDA_TRY(cudaEventElapsedTime(&total, c->ev_start, c->ev_copy));
+    const double t_synced = tracing ? now_seconds() : 0.0;
     if (blk) {
         // this rank's strips are in host memory (the event wait above); publish that, and rank 0 — whose caller
         // reads the frame — waits for every rank
@@ -683,6 +701,15 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
             for (int r = 1; r < c->world; r++)
                 if (!host_wait_word(&t->done[r], host_seq, 20.0))
                     return fail(RT_B200_ERR_STATE, "rank %d did not deliver its strips of frame %u (timeout)", r, host_seq);
+    }
+    if (tracing && blk) {
+        const double t_done = now_seconds();
+        c->trace[0] += t_issued - t_enter - t_go;   // enqueue kernels and copies
+        c->trace[1] += t_go;                        // waiting for rank 0 to enter the frame
+        c->trace[2] += t_synced - t_issued;         // waiting for the GPU (render + own copies)
+        c->trace[3] += t_done - t_synced;           // rank 0: waiting for the other ranks' strips
+        c->trace[4] += c->ms_render * 1e-3;
+        c->trace_frames++;
     }
     c->rendered = true;
     if (elapsed_ms) *elapsed_ms = total;
@@ -858,6 +885,12 @@ int rt_b200_gather(rt_b200_ctx *c, void *host_rgba8, size_t host_bytes, const vo
 
 int rt_b200_destroy(rt_b200_ctx *c)
 {
+    if (c && c->trace_frames) {
+        const double k = 1e6 / c->trace_frames;
+        std::fprintf(stderr, "[rt_b200 trace] rank %d: %u shared-host frames, per frame: enqueue %.1f us, wait go %.1f us, "
+                     "wait gpu %.1f us (render %.1f us), wait ranks %.1f us\n", c->rank, c->trace_frames,
+                     c->trace[0] * k, c->trace[1] * k, c->trace[2] * k, c->trace[4] * k, c->trace[3] * k);
+    }
     if (!c) return RT_B200_OK;
     cudaSetDevice(c->device);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
