@@ -192,6 +192,8 @@ struct rt_b200_ctx {
     int wave_variant = 0;
     int cubic_filter = 1;
     int cull_backfacing = 1;
+    bool sync_in_kernel = false;       // this frame's go / flag words are handled inside the wavefront kernel
+    bool tile_counter_dirty = false;   // another kernel used the tile counter: zero it before the wavefront kernel
     double trace[5] = {0, 0, 0, 0, 0};   // RT_B200_TRACE=1: seconds spent per stage of update_to_host (shared block)
     unsigned trace_frames = 0;
     bool cull_safe = true;           // every light / object colour is finite and moderate: 0 * colour is exactly 0
@@ -395,7 +397,8 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     up(upload(orig_index, &c->d_orig), "index map");
     up(upload(ldev, &c->d_lights), "lights");
     up(upload(cubic_mask, &c->d_cubic_mask), "cubic masks");
-    up(cudaMalloc((void **) &c->d_tile_counter, sizeof(unsigned long long)), "tile counter");
+    up(cudaMalloc((void **) &c->d_tile_counter, 2 * sizeof(unsigned long long)), "tile counter");
+    if (c->d_tile_counter) up(cudaMemset(c->d_tile_counter, 0, 2 * sizeof(unsigned long long)), "tile counter");
     c->sphere_r2_max = r2_max;
     // queue kernel tables: [2 + n_lights] rows of n_sphere_pad entries
     c->qtables.n_sphere_pad = ((int) sphere.size() + 3) & ~3;
@@ -497,11 +500,27 @@ int launch_kernel(rt_b200_ctx *c, const rt::FrameParams &f)
         ql.primary_safe = (fabs(f.origin[0]) < 1e9 && fabs(f.origin[1]) < 1e9 && fabs(f.origin[2]) < 1e9) ? 1 : 0;
         ql.shadow_cache = c->shadow_cache;
         ql.variant = c->queue_variant;
+        c->tile_counter_dirty = true;
         CUDA_TRY(rt::launch_render_queue(c->view, f, ql, c->stream));
     }
     else {   // kernel 1, and kernel 2 for scenes that exceed the queue kernel's parameter block
-        rt::WaveLaunch wl{c->d_tile_counter, c->d_cubic_mask, c->sphere_r2_max, c->shadow_cache, c->wave_variant, c->cubic_filter, (c->cull_backfacing && c->cull_safe) ? 1 : 0};
-        CUDA_TRY(rt::launch_render_wave(c->view, f, wl, c->stream));
+        if (c->tile_counter_dirty) {
+            CUDA_TRY(cudaMemsetAsync(c->d_tile_counter, 0, 2 * sizeof(unsigned long long), c->stream));
+            c->tile_counter_dirty = false;
+        }
+        rt::WaveLaunch wl{c->d_tile_counter, c->d_cubic_mask, c->sphere_r2_max, c->shadow_cache, c->wave_variant, c->cubic_filter,
+                          (c->cull_backfacing && c->cull_safe) ? 1 : 0, nullptr, nullptr, nullptr, 0u};
+        if (c->sync_in_kernel) {   // fused gather: the render kernel does the frame hand-shake itself
+            wl.sync_go = c->d_go;
+            wl.sync_flags = c->d_flags;
+            wl.sync_timed_out = c->d_timed_out;
+            wl.sync_seq = c->seq;
+        }
+        const cudaError_t e = rt::launch_render_wave(c->view, f, wl, c->stream);
+        if (e != cudaSuccess) {
+            c->tile_counter_dirty = true;
+            return fail(RT_B200_ERR_CUDA, "launch_render_wave: %s", cudaGetErrorString(e));
+        }
     }
     return RT_B200_OK;
 }
@@ -585,10 +604,14 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
 
     if (c->count) CUDA_TRY(cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long) * rt::CNT_COUNT, c->stream));
     CUDA_TRY(cudaEventRecord(c->ev_start, c->stream));
+    // kernel 1 does the go / flag hand-shake of the fused gather in its own prologue / epilogue: no extra launches
+    c->sync_in_kernel = shared && c->flag_barrier && (c->kernel_kind == 1 || (c->kernel_kind == 2 && !c->qscene));
     if (shared && c->flag_barrier) {
         c->seq++;
-        if (c->rank == 0) CUDA_TRY(rt::launch_sync_store(c->d_go, c->seq, c->stream));
-        else CUDA_TRY(rt::launch_sync_wait(c->d_go, 0, 1, c->seq - 1, c->d_timed_out, c->stream));
+        if (!c->sync_in_kernel) {
+            if (c->rank == 0) CUDA_TRY(rt::launch_sync_store(c->d_go, c->seq, c->stream));
+            else CUDA_TRY(rt::launch_sync_wait(c->d_go, 0, 1, c->seq - 1, c->d_timed_out, c->stream));
+        }
     }
     if (c->kernel_kind == 2 && c->qscene)   // the primary-ray table depends on the camera origin: one setup launch per frame
         CUDA_TRY(rt::build_queue_tables(c->view, c->qtables, *c->qscene, 1, 2, f.origin, c->stream));
@@ -654,8 +677,10 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
         if (shared && c->flag_barrier) {
             // every rank's pixels are already in rank 0's frame: each rank publishes "frame seq done" in rank 0's
             // memory, and only rank 0 — the consumer of the frame — waits for all of them
-            CUDA_TRY(rt::launch_sync_store(c->d_flags + c->rank, c->seq, c->stream));
-            if (c->rank == 0) CUDA_TRY(rt::launch_sync_wait(c->d_flags, 1, c->world - 1, c->seq, c->d_timed_out, c->stream));
+            if (!c->sync_in_kernel) {
+                CUDA_TRY(rt::launch_sync_store(c->d_flags + c->rank, c->seq, c->stream));
+                if (c->rank == 0) CUDA_TRY(rt::launch_sync_wait(c->d_flags, 1, c->world - 1, c->seq, c->d_timed_out, c->stream));
+            }
             c->last_frame = c->d_shared[c->parity];
         }
         else if (shared) {

@@ -57,13 +57,27 @@ struct WaveCtl {
     int prim_filter;             // rays only while enough of them miss for a proven miss to pay for the filter
 };
 
+// Frame synchronisation of the fused multi-GPU gather, done by the render kernel itself (no extra launches):
+//   prologue  rank 0 publishes go = seq; the other ranks wait for go >= seq - 1 before their first store into rank 0's
+//             frame (rank 0 may still be reading the frame that used this buffer two frames ago)
+//   epilogue  the last CTA to finish publishes flags[rank] = seq after a system-scope fence; on rank 0 it then
+//             waits until every rank's flag has reached seq, so the kernel's completion means "frame assembled"
+struct WaveSync {
+    unsigned *go;                // in rank 0's memory (null: no fused gather, nothing of this runs)
+    unsigned *flags;             // [world], in rank 0's memory
+    unsigned *timed_out;         // mapped host word
+    unsigned seq;
+    int rank, world;
+};
+
 struct WaveConfig {
     int tiles_x, tiles_y;        // 32 x (W/32) pixel tiles over [local_rows][width]
     int spheres_in_smem;
     int use_shadow_cache;
     int use_cubic_filter;
     int cull_backfacing;         // skip shadow rays of lights whose Lambert factor is 0 at the hit (they add exactly 0)
-    unsigned long long *tile_counter;
+    unsigned long long *tile_counter;   // [0] next tile, [1] CTAs finished; the last CTA leaves both at 0
+    WaveSync sync;
     const unsigned *cubic_mask;  // global copy
     float sphere_r2_max;
 };

@@ -103,6 +103,25 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
             s.light_d = ld;
             s.hit_o = reinterpret_cast<CubicO *>(sp);
         }
+        // fused gather: frame hand-shake with rank 0 (WaveSync) — before the first pixel leaves this GPU
+        if (cfg.sync.go != nullptr && tid == 0) {
+            if (cfg.sync.rank == 0) {
+                if (blockIdx.x == 0) asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(cfg.sync.go), "r"(cfg.sync.seq) : "memory");
+            }
+            else {
+                const long long t0 = clock64();
+                for (;;) {
+                    unsigned v;
+                    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(cfg.sync.go) : "memory");
+                    if ((int) (v - (cfg.sync.seq - 1u)) >= 0) break;
+                    if (clock64() - t0 > 40000000000LL) {   // ~20 s: report instead of hanging the box
+                        *cfg.sync.timed_out = 1u;
+                        break;
+                    }
+                    __nanosleep(100);
+                }
+            }
+        }
     }
     __syncthreads();
 
@@ -346,6 +365,39 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         __syncthreads();
     }
     if (COUNT) flush_tally(tl, f.counters);
+
+    // ---- end of launch: the last CTA re-arms the counters and, with the fused gather, signals "frame complete" ----
+    if (cfg.sync.go != nullptr) __threadfence_system();   // this thread's pixel stores, visible to rank 0's consumer
+    __syncthreads();
+    if (tid == 0) {
+        const unsigned long long done = atomicAdd(cfg.tile_counter + 1, 1ULL);
+        const bool last = done == (unsigned long long) gridDim.x - 1ULL;
+        if (last) {
+            cfg.tile_counter[0] = 0ULL;     // the next launch on this stream starts from tile 0 without a memset
+            cfg.tile_counter[1] = 0ULL;
+            if (cfg.sync.go != nullptr) {
+                __threadfence_system();
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(cfg.sync.flags + cfg.sync.rank), "r"(cfg.sync.seq) : "memory");
+            }
+        }
+        ctl.tile = last ? 1 : 0;
+    }
+    if (cfg.sync.go != nullptr && cfg.sync.rank == 0) {
+        __syncthreads();
+        if (ctl.tile && tid < cfg.sync.world) {   // rank 0 consumes the frame: wait for every rank's flag
+            const long long t0 = clock64();
+            for (;;) {
+                unsigned v;
+                asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(cfg.sync.flags + tid) : "memory");
+                if ((int) (v - cfg.sync.seq) >= 0) break;
+                if (clock64() - t0 > 40000000000LL) {
+                    *cfg.sync.timed_out = 1u;
+                    break;
+                }
+                __nanosleep(100);
+            }
+        }
+    }
 }
 
 namespace {
@@ -377,9 +429,7 @@ cudaError_t launch_wave_variant(const SceneView &scene, const FrameParams &frame
     const int n_tiles = cfg.tiles_x * cfg.tiles_y;
     int grid = n_sm * per_sm;
     if (grid > n_tiles) grid = n_tiles;
-    e = cudaMemsetAsync(cfg.tile_counter, 0, sizeof(unsigned long long), stream);
-    if (e != cudaSuccess) return e;
-    kern<<<grid, W, smem, stream>>>(scene, frame, cfg);
+    kern<<<grid, W, smem, stream>>>(scene, frame, cfg);   // tile counter: left at 0 by the previous launch's last CTA
     return cudaGetLastError();
 }
 
@@ -400,6 +450,7 @@ cudaError_t launch_render_wave(const SceneView &scene, const FrameParams &frame,
     WaveConfig cfg;
     cfg.tiles_x = cfg.tiles_y = 0;
     cfg.tile_counter = wl.tile_counter;
+    cfg.sync = WaveSync{wl.sync_go, wl.sync_flags, wl.sync_timed_out, wl.sync_seq, frame.rank, frame.world};
     cfg.cubic_mask = wl.cubic_mask;
     cfg.sphere_r2_max = wl.sphere_r2_max;
     cfg.use_shadow_cache = wl.shadow_cache >= 0 ? wl.shadow_cache : (scene.n_objects >= 8 ? 1 : 0);
