@@ -583,9 +583,7 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
     }
     if (streamed) {
         const size_t local_bytes = sizeof(uchar4) * (size_t) c->width * c->local_rows;
-        // one GPU: ~4 MB bands; several GPUs feeding one host frame: each rank's share is small, ~1 MB bands keep
-        // its copy engine busy while it still renders
-        n_bands = c->host_bands > 0 ? c->host_bands : (int) (local_bytes / (c->world > 1 ? (1u << 20) : (4u << 20)));
+        n_bands = c->host_bands > 0 ? c->host_bands : (int) (local_bytes / (4u << 20));   // measured: smaller bands do not pay, at 1 or 8 GPUs
         if (n_bands > RT_MAX_BANDS) n_bands = RT_MAX_BANDS;
         if (n_bands > (c->local_rows + band_unit - 1) / band_unit) n_bands = (c->local_rows + band_unit - 1) / band_unit;
         if (n_bands < 1) n_bands = 1;
