@@ -293,6 +293,24 @@ __device__ __forceinline__ d3 primary_dir(const FrameParams &f, const d3 &origin
     return normalize3(d3{v.x - origin.x, v.y - origin.y, v.z - origin.z});
 }
 
+// The same in two steps, for kernels that compute the per-column / per-row factors once per tile: cam_x depends only
+// on the pixel column, cam_y only on the image row (identical expressions, hence identical bits).
+__device__ __forceinline__ double primary_cam_x(const FrameParams &f, int px)
+{
+    double ndc_x = (px + 0.5) / f.width;
+    return (2.0 * ndc_x - 1.0) * f.aspect * f.tan_half_fov;
+}
+__device__ __forceinline__ double primary_cam_y(const FrameParams &f, int py)
+{
+    double ndc_y = (py + 0.5) / f.height;
+    return (2.0 * ndc_y - 1.0) * f.tan_half_fov;
+}
+__device__ __forceinline__ d3 primary_dir_cam(const FrameParams &f, const d3 &origin, double cam_x, double cam_y)
+{
+    d3 v = mat_point(f.m, cam_x, cam_y, 1.0, 1.0);
+    return normalize3(d3{v.x - origin.x, v.y - origin.y, v.z - origin.z});
+}
+
 // update-cuda.cu:149-156: (int)(c*255 + 0.5) per channel, alpha 255
 __device__ __forceinline__ uchar4 pack_rgba8(float r, float g, float b)
 {

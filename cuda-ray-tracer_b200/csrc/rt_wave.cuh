@@ -55,6 +55,7 @@ struct WaveCtl {
     int occ_found[2];            // occluders found so far by [0] the sphere pass, [1] the cubic pass
     int prim_rays, prim_hits;    // recent primary rays / hits of this CTA (decayed): the cubic filter runs on primary
     int prim_filter;             // rays only while enough of them miss for a proven miss to pay for the filter
+    double cam_x[32], cam_y[MAX_WARPS];   // camera-plane coordinates of the current tile's 32 columns / W/32 rows
 };
 
 // Frame synchronisation of the fused multi-GPU gather, done by the render kernel itself (no extra launches):

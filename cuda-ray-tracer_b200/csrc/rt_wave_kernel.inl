@@ -156,6 +156,17 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
             if (!tiles_left) break;
             continue;   // unreachable in practice: tile < 0 with tiles_left means pool >= WAVE
         }
+        if (tile >= 0 && tid < 32 + TILE_ROWS) {
+            // the two divisions of primary ray generation (update-cpu.cpp:84-87) once per column / row of the tile
+            const int tx = tile % cfg.tiles_x, ty = tile / cfg.tiles_x;
+            if (tid < 32) {
+                ctl.cam_x[tid] = primary_cam_x(f, tx * 32 + tid);
+            }
+            else {
+                const int lrow = f.row0 + ty * TILE_ROWS + (tid - 32);
+                ctl.cam_y[tid - 32] = primary_cam_y(f, local_to_image_row(lrow, f.strip_rows, f.rank, f.world));
+            }
+        }
         __syncthreads();   // everyone has read ctl.tile / pool_count before they change
 
         // ---- ray of this thread -----------------------------------------------------------------------
@@ -175,7 +186,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
             if (in_buf && !active && !f.direct) f.out[pixel] = make_uchar4(0, 0, 0, 0);   // padding row past the image
             if (active) {
                 o = cam_origin;
-                d = primary_dir(f, cam_origin, x, y);
+                d = primary_dir_cam(f, cam_origin, ctl.cam_x[(warp & 3) * 8 + (lane & 7)], ctl.cam_y[(warp >> 2) * 4 + (lane >> 3)]);
                 if (COUNT) tl.n[CNT_PRIMARY]++;
             }
         }
@@ -206,6 +217,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
                 const d3 n = surface_normal(g.coef_full + 20 * obj, p);
                 wh.px[tid] = p.x; wh.py[tid] = p.y; wh.pz[tid] = p.z;
                 wh.nx[tid] = n.x; wh.ny[tid] = n.y; wh.nz[tid] = n.z;
+                wh.occluded[tid] = 0u;
                 if (CUBIC && s.hit_o && cfg.use_cubic_filter)   // origin half of the filter, shared by this hit's shadow rays
                     s.hit_o[tid] = make_cubic_o(s.cubic_f, (float) (p.x + RT_SHADOW_BIAS * n.x), (float) (p.y + RT_SHADOW_BIAS * n.y),
                                                 (float) (p.z + RT_SHADOW_BIAS * n.z));
@@ -246,8 +258,10 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         if (hit) mat = __ldg(&g.material[obj]);
         for (int l0 = 0; l0 < g.n_lights; l0 += LIGHT_CHUNK) {
             const int lc = min(LIGHT_CHUNK, g.n_lights - l0);
-            if (hit) wh.occluded[tid] = 0u;
-            __syncthreads();
+            if (l0 > 0) {   // first chunk: cleared with the hit record, before the barrier that published the records
+                if (hit) wh.occluded[tid] = 0u;
+                __syncthreads();
+            }
             // C: task = (light j, hit i), light-major
             const unsigned inv_hits = n_hits > 1 ? (unsigned) ((0x100000000ULL + n_hits - 1) / (unsigned) n_hits) : 0u;   // ceil(2^32 / n)
             const bool lone_cubic = CUBIC && s.hit_o != nullptr && cfg.use_cubic_filter && g.n_objects == 1;
@@ -312,7 +326,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
                 }
                 acc_r = acc.x; acc_g = acc.y; acc_b = acc.z;
             }
-            __syncthreads();
+            if (l0 + LIGHT_CHUNK < g.n_lights) __syncthreads();   // the next chunk reuses the occlusion words
         }
 
         // ---- phase D (part 2): clamp, blend, bounce ---------------------------------------------------------------
