@@ -100,10 +100,12 @@ __host__ __device__ inline size_t wave_scene_smem(const SceneView &sc, bool sphe
 
 // filter caches behind the scene arrays: per cubic the camera-origin half; for single-cubic scenes also the per-light
 // direction halves and one origin half per wave slot (the shadow origin of that slot's hit)
+__host__ __device__ inline bool wave_single_cubic(const SceneView &sc) { return sc.n_cubic == 1 && sc.n_lights <= 256; }
+
 __host__ __device__ inline size_t wave_cubic_smem(const SceneView &sc, int wave)
 {
     size_t n = align16(sizeof(CubicO) * sc.n_cubic);
-    if (sc.n_cubic == 1) n += align16(sizeof(CubicD) * sc.n_lights) + align16(sizeof(CubicO) * wave);
+    if (wave_single_cubic(sc)) n += align16(sizeof(CubicD) * sc.n_lights) + align16(sizeof(CubicO) * wave);
     return n;
 }
 

@@ -93,7 +93,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         s.cam_o = co;
         s.light_d = nullptr;
         s.hit_o = nullptr;
-        if (CUBIC && g.n_cubic == 1) {
+        if (CUBIC && wave_single_cubic(g)) {
             CubicD *ld = reinterpret_cast<CubicD *>(sp);
             sp += align16(sizeof(CubicD) * g.n_lights);
             for (int j = tid; j < g.n_lights; j += WAVE) {

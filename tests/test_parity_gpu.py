@@ -291,3 +291,55 @@ def test_shared_host_frame_ranks_as_processes(pkg, rt, scenes_dir, tmp_path, wor
             if p.is_alive():
                 p.kill()
         rt.host_free_shared(ptr)
+
+
+def test_cubic_filter_and_culling_paths(pkg, rt, oracle):
+    """Kernel 1's FP32 cubic filter (cached halves / generic path / many lights) and the light culling: with every
+    combination of the two options the frame equals the exact kernel's, and the oracle's."""
+    from cuda_ray_tracer_b200 import camera
+    from cuda_ray_tracer_b200 import scene as S
+    bg = np.array([0.1, 0.2, 0.3], dtype=np.float32)
+    rng = np.random.default_rng(5)
+
+    def lights(n):
+        out = []
+        for i in range(n):
+            v = rng.normal(size=3)
+            if i % 3 == 0:
+                out.append(S.light_spherical(200.0 / n + 20.0, list(4.0 * v + np.array([0.0, 3.0, 4.0])), [1, 0.9, 0.8]))
+            else:
+                out.append(S.light_directional(3.0 / n + 0.2, list(v), [0.8, 0.9, 1.0]))
+        return np.array(out, dtype=S.LIGHT_DTYPE)
+
+    ding = S.surface_polynomial({"y3": 1.0, "x2": 1.0, "y2": -1.0, "z2": 1.0, "z": -20.0, "c": 100.0})
+    cases = {
+        "one cubic, cached halves": ([S.make_object(S.surface_cayley(), 0.3, (0.8, 0.7, 0.6))], lights(5)),
+        "one cubic, 300 lights (no per-light cache, 10 light chunks)": ([S.make_object(ding, 0.0, (0.7, 0.7, 0.9))], lights(300)),
+        "two cubics and a sphere": ([S.make_object(S.surface_clebsch(), 0.0, (0.9, 0.5, 0.5)),
+                                     S.make_object(ding, 0.4, (0.5, 0.9, 0.5)),
+                                     S.make_object(S.surface_sphere([0.5, 0.5, 6.0], 1.0), 0.2, (0.5, 0.5, 0.9))], lights(7)),
+    }
+    for label, (objs, ls) in cases.items():
+        sc = S.Scene(96, 54, np.radians(50.0), bg, 3)
+        sc.objects = np.array(objs, dtype=S.OBJECT_DTYPE)
+        sc.lights = ls
+        port = oracle.PortOracle(sc)
+        with rt.Renderer(sc) as r:
+            for pose in ("identity", "pose_a"):
+                m = camera.TEST_POSES[pose]
+                r.set_option("kernel", 0)
+                r.update(m)
+                exact = r.gather()
+                assert_parity(exact, oracle.quantize_rgba8(port.render(m, threads=os.cpu_count())), label + " exact kernel")
+                r.set_option("kernel", 1)
+                seen = {}
+                for filt in (0, 1):
+                    for cull in (0, 1):
+                        r.set_option("cubic_filter", filt)
+                        r.set_option("cull_backfacing", cull)
+                        r.update(m)
+                        assert np.array_equal(r.gather(), exact), (label, pose, filt, cull)
+                        seen[(filt, cull)] = r.counters()
+                assert seen[(1, 0)]["cubic_exact"] <= seen[(0, 0)]["cubic_exact"]
+                assert seen[(1, 1)]["shadow_rays"] <= seen[(1, 0)]["shadow_rays"]
+                assert seen[(0, 0)]["shadow_rays"] == seen[(0, 0)]["hits"] * len(ls)
