@@ -1000,7 +1000,7 @@ int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
         }
     }
     else if (!std::strcmp(name, "variant")) {
-        if (value < 0 || value > 5) return fail(RT_B200_ERR_ARG, "variant must be 0..5");
+        if (value != 0 && value != 2 && value != 3 && value != 5) return fail(RT_B200_ERR_ARG, "variant must be 0, 2, 3 or 5");
         c->wave_variant = (int) value;
     }
     else if (!std::strcmp(name, "queue_variant")) {

@@ -15,7 +15,7 @@ struct WaveLaunch {
     const unsigned *cubic_mask;         // device, [n_cubic] non-zero coefficient masks
     float sphere_r2_max;                // max r^2 over sphere-class objects (filter error bound)
     int shadow_cache;                   // 1 / 0 / -1 = automatic (on when the scene has >= 8 objects)
-    int variant;                        // 0 = automatic; 1/2/3 = 256-thread CTAs, min 1/2/3 per SM; 5 = 512-thread CTA
+    int variant;                        // 0 = automatic; 2 / 3 = 256-thread CTAs, two / three per SM; 5 = one 512-thread CTA
     int cubic_filter;                   // 1 = FP32 filter in front of the exact cubic test (rt_cubic_filter.cuh)
     int cull_backfacing;                // 1 = no shadow ray towards a light whose Lambert factor is 0 at the hit
     // fused multi-GPU gather: sequence words in rank 0's memory (go == nullptr: none), see WaveSync in rt_wave.cuh

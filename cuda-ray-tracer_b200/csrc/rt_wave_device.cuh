@@ -1,0 +1,213 @@
+// rt_wave_device.cuh — device functions of the wavefront kernel (phases A and C), shared by the two translation
+// units that instantiate it: rt_wave.cu (scenes with cubic-class objects) and rt_wave_plain.cu (scenes without).
+#ifndef RT_WAVE_DEVICE_CUH
+#define RT_WAVE_DEVICE_CUH
+
+#include "rt_kernels.h"
+#include "rt_wave.cuh"
+
+namespace rt {
+
+namespace {
+
+// ---- phase A: nearest hit (update-cpu.cpp:48-56) ---------------------------------------------------------
+// CUBIC = false compiles the cubic class out (scenes without cubics run a leaner kernel).
+template <bool CUBIC>
+__device__ __forceinline__ Hit nearest_hit_wave(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg,
+                                                const d3 &o, const d3 &d, bool primary, bool filter, Tally &tl)
+{
+    Hit h;
+    h.t = CUDART_INF;
+    h.slot = -1;
+    h.orig = 0x7fffffff;
+    int slot = 0;
+    for (int i = 0; i < g.n_plane; i++, slot++) consider_lazy(h, intersect_plane(s.plane[i], o, d), slot, g.orig_index);
+    if (g.n_sphere > 0) {
+        const RayF rf = make_rayf(o, d, g.sphere_center_max, cfg.sphere_r2_max);
+        unsigned confirms = 0;
+        const int n4 = rf.safe ? (g.n_sphere & ~3) : 0;
+        int i = 0;
+        for (; i < n4; i += 4) {
+            // four independent filter evaluations, one branch: candidates are rare
+            const float s0 = sphere_slack(rf, s.sphere_f[i]), s1 = sphere_slack(rf, s.sphere_f[i + 1]);
+            const float s2 = sphere_slack(rf, s.sphere_f[i + 2]), s3 = sphere_slack(rf, s.sphere_f[i + 3]);
+            if (!(fmaxf(fmaxf(s0, s1), fmaxf(s2, s3)) < 0.0f)) {
+#pragma unroll 1
+                for (int j = i; j < i + 4; j++) {
+                    if (!sphere_rejected<false>(rf, s.sphere_f[j])) {
+                        confirms++;
+                        consider_lazy(h, intersect_sphere(g.sphere[j], o, d), slot + j, g.orig_index);
+                    }
+                }
+            }
+        }
+        for (; i < g.n_sphere; i++) {
+            if (!rf.safe || !sphere_rejected<false>(rf, s.sphere_f[i])) {
+                confirms++;
+                consider_lazy(h, intersect_sphere(g.sphere[i], o, d), slot + i, g.orig_index);
+            }
+        }
+        slot += g.n_sphere;
+        tl.n[CNT_CONFIRM] += confirms;
+    }
+    for (int i = 0; i < g.n_quadric; i++, slot++)
+        consider_lazy(h, intersect_quadric(s.quadric + 10 * i, o, d), slot, g.orig_index);
+    if (CUBIC && g.n_cubic > 0) {
+        // FP32 filter first: a proven miss needs no FP64 expansion and no cbrt/acos/cos (rt_cubic_filter.cuh).
+        // Primary rays share the origin, so their origin half comes from the per-CTA cache.
+        const float ofx = (float) o.x, ofy = (float) o.y, ofz = (float) o.z;
+        const float dfx = (float) d.x, dfy = (float) d.y, dfz = (float) d.z;
+        unsigned exact = 0;
+        for (int i = 0; i < g.n_cubic; i++, slot++) {
+            if (cfg.use_cubic_filter && filter) {
+                const float *kf = s.cubic_f + RT_CF_FLOATS * i;
+                const CubicD cd = make_cubic_d(kf, dfx, dfy, dfz);
+                const int v = primary ? cubic_verdict_od(s.cam_o[i], cd, (float) RT_MAX_T, false)
+                                      : cubic_verdict_od(make_cubic_o(kf, ofx, ofy, ofz), cd, (float) RT_MAX_T, false);
+                if (v == CV_MISS) continue;
+            }
+            exact++;
+            consider_lazy(h, intersect_cubic_masked(s.cubic + 20 * i, s.cubic_mask[i], o, d), slot, g.orig_index);
+        }
+        tl.n[CNT_CUBIC_EXACT] += exact;
+    }
+    if (h.slot >= 0) h.orig = __ldg(&g.orig_index[h.slot]);
+    tl.n[CNT_T_PLANE] += g.n_plane;
+    tl.n[CNT_T_SPHERE] += g.n_sphere;
+    tl.n[CNT_T_QUADRIC] += g.n_quadric;
+    if (CUBIC) tl.n[CNT_T_CUBIC] += g.n_cubic;
+    return h;
+}
+
+// exact test of one class-sorted slot (shadow cache probe)
+template <bool CUBIC>
+__device__ __forceinline__ double intersect_slot(const SceneView &g, const SceneSmem &s, int slot, const d3 &o,
+                                                 const d3 &d, Tally &tl)
+{
+    if (slot < g.n_plane) {
+        tl.n[CNT_T_PLANE]++;
+        return intersect_plane(s.plane[slot], o, d);
+    }
+    slot -= g.n_plane;
+    if (slot < g.n_sphere) {
+        tl.n[CNT_T_SPHERE]++;
+        tl.n[CNT_CONFIRM]++;
+        return intersect_sphere(g.sphere[slot], o, d);
+    }
+    slot -= g.n_sphere;
+    if (slot < g.n_quadric) {
+        tl.n[CNT_T_QUADRIC]++;
+        return intersect_quadric(s.quadric + 10 * slot, o, d);
+    }
+    slot -= g.n_quadric;
+    if (!CUBIC) return -1.0;
+    tl.n[CNT_T_CUBIC]++;
+    tl.n[CNT_CUBIC_EXACT]++;
+    return intersect_cubic_masked(s.cubic + 20 * slot, s.cubic_mask[slot], o, d);
+}
+
+// ---- phase C: any occluder with EPS < t < max_t (update-cpu.cpp:66-72); returns the occluding slot or -1 ----
+// The boolean is order-independent, so classes are visited cheapest-first, except that the cubic class moves
+// in front of the sphere class while cubics are the more productive occluders per unit of work (block-local
+// statistics in WaveCtl::occ_found, updated as occluders are found).
+template <bool SEGMENT01>
+__device__ __forceinline__ int occluder_spheres(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg,
+                                                const d3 &o, const d3 &d, double max_t, Tally &tl)
+{
+    const int slot = g.n_plane;
+    const RayF rf = make_rayf(o, d, g.sphere_center_max, cfg.sphere_r2_max);
+    int found = -1;
+    const int n4 = rf.safe ? (g.n_sphere & ~3) : 0;
+    int i = 0;
+    for (; i < n4 && found < 0; i += 4) {
+        const float s0 = sphere_slack(rf, s.sphere_f[i]), s1 = sphere_slack(rf, s.sphere_f[i + 1]);
+        const float s2 = sphere_slack(rf, s.sphere_f[i + 2]), s3 = sphere_slack(rf, s.sphere_f[i + 3]);
+        if (!(fmaxf(fmaxf(s0, s1), fmaxf(s2, s3)) < 0.0f)) {
+#pragma unroll 1
+            for (int j = i; j < i + 4; j++) {
+                if (!sphere_rejected<SEGMENT01>(rf, s.sphere_f[j])) {
+                    tl.n[CNT_CONFIRM]++;
+                    if (blocks(intersect_sphere(g.sphere[j], o, d), max_t)) {
+                        found = slot + j;
+                        break;
+                    }
+                }
+            }
+        }
+    }
+    for (; i < g.n_sphere && found < 0; i++) {
+        if (!rf.safe || !sphere_rejected<SEGMENT01>(rf, s.sphere_f[i])) {
+            tl.n[CNT_CONFIRM]++;
+            if (blocks(intersect_sphere(g.sphere[i], o, d), max_t)) found = slot + i;
+        }
+    }
+    tl.n[CNT_T_SPHERE] += i;
+    return found;
+}
+
+// hit_slot / light: wave slot of the hit this shadow ray starts from and index of the light it goes to, the keys of
+// the filter caches (SceneSmem::hit_o, light_d) that exist when the scene has exactly one cubic.
+__device__ __forceinline__ int occluder_cubics(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg, const d3 &o,
+                                               const d3 &d, double max_t, int hit_slot, int light, Tally &tl)
+{
+    const int base = g.n_plane + g.n_sphere + g.n_quadric;
+    const float hi = (float) max_t;   // 1 or 1e6, both exact in FP32
+    const float dfx = (float) d.x, dfy = (float) d.y, dfz = (float) d.z;
+    if (cfg.use_cubic_filter && s.hit_o) {
+        tl.n[CNT_T_CUBIC]++;
+        // point light: the direction differs per hit; directional light: cached per light
+        const CubicD cd = (hi == 1.0f) ? make_cubic_d(s.cubic_f, dfx, dfy, dfz) : s.light_d[light];
+        const int v = cubic_verdict_od(s.hit_o[hit_slot], cd, hi, true);
+        if (v == CV_MISS) return -1;
+        if (v == CV_HIT) return base;
+        tl.n[CNT_CUBIC_EXACT]++;
+        return blocks(intersect_cubic_masked(s.cubic, s.cubic_mask[0], o, d), max_t) ? base : -1;
+    }
+    const float ofx = (float) o.x, ofy = (float) o.y, ofz = (float) o.z;
+    for (int i = 0; i < g.n_cubic; i++) {
+        tl.n[CNT_T_CUBIC]++;
+        if (cfg.use_cubic_filter) {
+            const float *kf = s.cubic_f + RT_CF_FLOATS * i;
+            const int v = cubic_verdict_od(make_cubic_o(kf, ofx, ofy, ofz), make_cubic_d(kf, dfx, dfy, dfz), hi, true);
+            if (v == CV_MISS) continue;
+            if (v == CV_HIT) return base + i;
+        }
+        tl.n[CNT_CUBIC_EXACT]++;
+        if (blocks(intersect_cubic_masked(s.cubic + 20 * i, s.cubic_mask[i], o, d), max_t)) return base + i;
+    }
+    return -1;
+}
+
+template <bool SEGMENT01, bool CUBIC>
+__device__ __forceinline__ int occluder_wave(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg, WaveCtl &ctl,
+                                             const d3 &o, const d3 &d, double max_t, int hit_slot, int light, Tally &tl)
+{
+    for (int i = 0; i < g.n_plane; i++) {
+        tl.n[CNT_T_PLANE]++;
+        if (blocks(intersect_plane(s.plane[i], o, d), max_t)) return i;
+    }
+    const int quad_base = g.n_plane + g.n_sphere;
+    for (int i = 0; i < g.n_quadric; i++) {
+        tl.n[CNT_T_QUADRIC]++;
+        if (blocks(intersect_quadric(s.quadric + 10 * i, o, d), max_t)) return quad_base + i;
+    }
+    if (g.n_sphere == 0) return (CUBIC && g.n_cubic) ? occluder_cubics(g, s, cfg, o, d, max_t, hit_slot, light, tl) : -1;
+    if (!CUBIC || g.n_cubic == 0) return occluder_spheres<SEGMENT01>(g, s, cfg, o, d, max_t, tl);
+    // relative cost of a full pass: ~4 issue slots x 4 per sphere filter, ~600 per exact cubic test
+    const volatile int *found = ctl.occ_found;
+    const bool cubic_first = (long long) found[1] * (16LL * g.n_sphere) > (long long) found[0] * (600LL * g.n_cubic);
+    int by = cubic_first ? occluder_cubics(g, s, cfg, o, d, max_t, hit_slot, light, tl) : occluder_spheres<SEGMENT01>(g, s, cfg, o, d, max_t, tl);
+    if (by >= 0) {
+        atomicAdd(&ctl.occ_found[cubic_first ? 1 : 0], 1);
+        return by;
+    }
+    by = cubic_first ? occluder_spheres<SEGMENT01>(g, s, cfg, o, d, max_t, tl) : occluder_cubics(g, s, cfg, o, d, max_t, hit_slot, light, tl);
+    if (by >= 0) atomicAdd(&ctl.occ_found[cubic_first ? 0 : 1], 1);
+    return by;
+}
+
+} // namespace
+
+} // namespace rt
+
+#endif

@@ -416,20 +416,16 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
 
 namespace {
 
-template <int W, int MINB>
+template <int W, int MINB, bool CUBIC>
 cudaError_t launch_wave_variant(const SceneView &scene, const FrameParams &frame, WaveConfig cfg, size_t scene_smem,
                                 int n_sm, int max_smem, cudaStream_t stream)
 {
     static bool attr_set = false;
-    const bool cubic = scene.n_cubic > 0;
-    auto kern = cubic ? (frame.counters ? render_wave_kernel<W, MINB, true, true> : render_wave_kernel<W, MINB, false, true>)
-                      : (frame.counters ? render_wave_kernel<W, MINB, true, false> : render_wave_kernel<W, MINB, false, false>);
+    auto kern = frame.counters ? render_wave_kernel<W, MINB, true, CUBIC> : render_wave_kernel<W, MINB, false, CUBIC>;
     cudaError_t e;
     if (!attr_set) {
-        e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, true, CUBIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, false, CUBIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
@@ -447,11 +443,11 @@ cudaError_t launch_wave_variant(const SceneView &scene, const FrameParams &frame
     return cudaGetLastError();
 }
 
-} // namespace
-
-// Variant choice: 256-thread CTAs, two (or three) per SM, while the staged scene leaves room for that; otherwise
-// one 512-thread CTA per SM so that a large scene is staged once and still 16 warps are resident.
-cudaError_t launch_render_wave(const SceneView &scene, const FrameParams &frame, const WaveLaunch &wl, cudaStream_t stream)
+// Variant choice: 256-thread CTAs, three per SM, while the staged scene leaves room for that; otherwise one
+// 512-thread CTA per SM so that a large scene is staged once and still 16 warps are resident.  (256 x {1, 4} were
+// measured in round 1 and never won; they are no longer compiled.)
+template <bool CUBIC>
+cudaError_t launch_render_wave_t(const SceneView &scene, const FrameParams &frame, const WaveLaunch &wl, cudaStream_t stream)
 {
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
@@ -481,13 +477,13 @@ cudaError_t launch_render_wave(const SceneView &scene, const FrameParams &frame,
     int variant = wl.variant;
     if (variant <= 0) variant = (3 * cta256 <= (size_t) sm_smem) ? 3 : 5;
     switch (variant) {
-        case 1: return launch_wave_variant<256, 1>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
-        case 2: return launch_wave_variant<256, 2>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
-        case 3: return launch_wave_variant<256, 3>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
-        case 4: return launch_wave_variant<256, 4>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
-        case 5: return launch_wave_variant<512, 1>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
+        case 2: return launch_wave_variant<256, 2, CUBIC>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
+        case 3: return launch_wave_variant<256, 3, CUBIC>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
+        case 5: return launch_wave_variant<512, 1, CUBIC>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
         default: return cudaErrorInvalidValue;
     }
 }
+
+} // namespace
 
 } // namespace rt

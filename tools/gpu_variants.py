@@ -9,7 +9,7 @@ from cuda_ray_tracer_b200 import binding, camera, synth
 names = ["20spheres", "quadratic", "cubic", "cayley", "clebsch", "dingdong", "monkey_saddle", "reflection_test"]
 todo = [(n, pkg.load_from_file(os.path.join(ROOT, "scenes", n + ".yml")).with_overrides(width=3840, height=2160, max_reflections=4)) for n in names]
 todo.append(("synthetic_960x540", synth.synthetic_scene(width=960, height=540)))
-variants = [int(v) for v in sys.argv[1].split(",")] if len(sys.argv) > 1 else [1, 2, 3, 5]
+variants = [int(v) for v in sys.argv[1].split(",")] if len(sys.argv) > 1 else [2, 3, 5]
 opts = {}
 for a in sys.argv[2:]:
     k, v = a.split("=")
