@@ -20,9 +20,12 @@
 //   2. Degree switches (surface_impl.h:106,138,150): a branch is certain when |T_i| - E_i > 1e-7 or |T_i| + E_i < 1e-7;
 //      the lower-degree branches drop the higher coefficients exactly as the reference does.  For the quadratic
 //      branch with t2 < 0 the reference tries the LARGER root first, so only a downward crossing proves a hit.
-//   3. The reference's own root error is ~64 u64 M with M = 4 max(|t2/t3|, sqrt|t1/t3|, cbrt|t0/t3|); requiring
-//      |t2| < 1e6 |t3|, |t1| < 1e12 |t3|, |t0| < 1e18 |t3| keeps it below EPS / 2 = 5e-8, which is the slack the
-//      interval ends get below (factor 2 around EPS, 2e-6 relative around hi).
+//   3. The reference's own root error is ~64 u64 M with M = 4 max(|t2/t3|, sqrt|t1/t3|, cbrt|t0/t3|) (more in the
+//      trigonometric branch near delta = 0, which 3b excludes); requiring |t2| < 1e4 |t3|, |t1| < 1e8 |t3|,
+//      |t0| < 1e12 |t3| keeps it below EPS / 2 = 5e-8, which is the slack the interval ends get below (factor 2
+//      around EPS, 2e-6 relative around hi).
+//   3b. The reference's choice between Cardano and the trigonometric formula must not hinge on FP64 rounding: the
+//      sign of the normalised discriminant has to be certifiable in FP32 (see the code).
 //   4. With s = sign(T0), for all t >= 0:  s P(t) >= g(t) and s P(t) <= h(t), where g, h are the cubics with
 //      coefficients s T_i -/+ E_i — EXACTLY known polynomials, so their extrema over an interval sit at its ends
 //      and at their own critical points, which a compensated discriminant (Kahan) locates to a few ulps; a
@@ -227,13 +230,44 @@ RT_HD int cubic_verdict_tb(float T[4], const float B[4], float hi, bool want_hit
     if (deg < 3) { T[3] = 0.0f; E[3] = 0.0f; }          // the reference drops the higher coefficients altogether
     if (deg < 2) { T[2] = 0.0f; E[2] = 0.0f; }
     // 3. the reference's own roots are accurate to well below EPS / 2: with the leading coefficient L (degree 3 or 2)
-    //    |next| < 1e6 L, |next but one| < 1e12 L, |last| < 1e18 L
+    //    |next| < 1e4 L, |next but one| < 1e8 L, |last| < 1e12 L, i.e. every root and every intermediate of the closed
+    //    forms is below ~4e4 in magnitude (with 3b: trigonometric-branch roots are then good to ~1e-8)
     {
         const float lead = (deg == 3 ? fabsf(T[3]) - E[3] : fabsf(T[2]) - E[2]);
         const float n1 = (deg == 3 ? fabsf(T[2]) + E[2] : fabsf(T[1]) + E[1]);
         const float n2 = (deg == 3 ? fabsf(T[1]) + E[1] : fabsf(T[0]) + E[0]);
         const float n3 = (deg == 3 ? fabsf(T[0]) + E[0] : 0.0f);
-        ok = ok && (deg == 1 || (n1 < 1e6f * lead && n2 < 1e12f * lead && n3 < 1e18f * lead));
+        ok = ok && (deg == 1 || (n1 < 1e4f * lead && n2 < 1e8f * lead && n3 < 1e12f * lead));
+    }
+    // 3b. cubic branch: the reference chooses between Cardano and the trigonometric formula by the sign of
+    //    delta = q^3 + r^2 of the NORMALISED cubic (surface_impl.h:112-116).  Two roots that are close relative to the
+    //    largest root magnitude (e.g. a nearly quadratic ray: third root far away at -t2/t3) make that sign a matter
+    //    of FP64 rounding — the reference may then return the far root and ignore a crossing that P really has, or the
+    //    other way round.  Nothing can be predicted there, so a verdict needs the sign of delta CERTIFIED in FP32:
+    //    |delta| > 2 e_delta + 1e-12 (Qs^3 + Rs^2), with first-order error propagation through a_i = T_i / T_3.
+    if (deg == 3) {
+        const float inv = RT_CF_DIV(1.0f, T[3]);            // a few ulps: covered by the 4 u terms below
+        const float x3 = E[3] * fabsf(inv);                 // relative error of T3; 1 / (1 - x) <= 1 + 1.34 x for x <= 1/4
+        const float ainv = fabsf(inv) * fmaf(1.34f, x3, 1.0002f);
+        const float a2 = T[2] * inv, a1 = T[1] * inv, a0 = T[0] * inv;
+        const float e2a = fmaf(fmaf(fabsf(a2), E[3], E[2]), ainv, 4.0f * RT_CF_U * fabsf(a2));
+        const float e1a = fmaf(fmaf(fabsf(a1), E[3], E[1]), ainv, 4.0f * RT_CF_U * fabsf(a1));
+        const float e0a = fmaf(fmaf(fabsf(a0), E[3], E[0]), ainv, 4.0f * RT_CF_U * fabsf(a0));
+        const float A2 = fabsf(a2) + e2a, A1 = fabsf(a1) + e1a;   // upper bounds of the true |a_i|
+        const float a22 = a2 * a2;
+        const float q = fmaf(3.0f, a1, -a22) * (1.0f / 9.0f);
+        const float qs = fmaf(3.0f, fabsf(a1), a22) * (1.0f / 9.0f);
+        const float eq = fmaf(fmaf(2.0f * A2, e2a, 3.0f * e1a), 1.0f / 9.0f, 8.0f * RT_CF_U * qs);
+        const float a21 = a2 * a1;
+        const float r = fmaf(-2.0f * a22, a2, fmaf(9.0f, a21, -27.0f * a0)) * (1.0f / 54.0f);
+        const float rs = fmaf(2.0f * a22, fabsf(a2), fmaf(9.0f, fabsf(a21), 27.0f * fabsf(a0))) * (1.0f / 54.0f);
+        const float er = fmaf(fmaf(6.0f * A2 * A2, e2a, fmaf(9.0f, fmaf(A2, e1a, A1 * e2a), 27.0f * e0a)), 1.0f / 54.0f,
+                              8.0f * RT_CF_U * rs);
+        const float delta = fmaf(q * q, q, r * r);
+        const float scale = fmaf(qs * qs, qs, rs * rs);
+        const float Q = fabsf(q) + eq, R = fabsf(r) + er;
+        const float ed = fmaf(3.0f * Q * Q, eq, fmaf(2.0f * R, er, 8.0f * RT_CF_U * scale));
+        ok = ok && x3 < 0.25f && fabsf(delta) > fmaf(2.0f, ed, 1e-12f * scale) && scale < 1e37f;
     }
     // 4. sign-normalised lower polynomial g = s T - E <= s P
     const float s = T[0] > 0.0f ? 1.0f : -1.0f;
