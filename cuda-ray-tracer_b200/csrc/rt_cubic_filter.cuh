@@ -21,8 +21,9 @@
 //      the lower-degree branches drop the higher coefficients exactly as the reference does.  For the quadratic
 //      branch with t2 < 0 the reference tries the LARGER root first, so only a downward crossing proves a hit.
 //   3. The reference's own root error is ~64 u64 M with M = 4 max(|t2/t3|, sqrt|t1/t3|, cbrt|t0/t3|) (more in the
-//      trigonometric branch near delta = 0, which 3b excludes); requiring |t2| < 1e4 |t3|, |t1| < 1e8 |t3|,
-//      |t0| < 1e12 |t3| keeps it below EPS / 2 = 5e-8, which is the slack the interval ends get below (factor 2
+//      trigonometric branch near delta = 0, which 3b excludes); a per-ray bound of
+//      that error (3c in the code: cancellation in Cardano's r - sqrt(delta) when q is small, acos near +-1 in the
+//      trigonometric branch) must stay below EPS / 4 = 2.5e-8, inside the slack the interval ends get below (factor 2
 //      around EPS, 2e-6 relative around hi).
 //   3b. The reference's choice between Cardano and the trigonometric formula must not hinge on FP64 rounding: the
 //      sign of the normalised discriminant has to be certifiable in FP32 (see the code).
@@ -208,9 +209,11 @@ RT_HD float cf_sqrt(float x)
     asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
+RT_HD float cf_cbrt(float x) { return exp2f(__log2f(x) * 0.33333334f); }   // x > 0; ~1e-6 relative, used in bounds only
 #else
 #define RT_CF_DIV(x, y) ((x) / (y))
 RT_HD float cf_sqrt(float x) { return sqrtf(x); }
+RT_HD float cf_cbrt(float x) { return cbrtf(x); }
 #endif
 
 // The decision from the FP32 coefficients T[i] (index = power of t) and the sums of absolute values B[i].
@@ -229,15 +232,11 @@ RT_HD int cubic_verdict_tb(float T[4], const float B[4], float hi, bool want_hit
     const int deg = c3 ? 3 : (c2 ? 2 : 1);
     if (deg < 3) { T[3] = 0.0f; E[3] = 0.0f; }          // the reference drops the higher coefficients altogether
     if (deg < 2) { T[2] = 0.0f; E[2] = 0.0f; }
-    // 3. the reference's own roots are accurate to well below EPS / 2: with the leading coefficient L (degree 3 or 2)
-    //    |next| < 1e4 L, |next but one| < 1e8 L, |last| < 1e12 L, i.e. every root and every intermediate of the closed
-    //    forms is below ~4e4 in magnitude (with 3b: trigonometric-branch roots are then good to ~1e-8)
-    {
-        const float lead = (deg == 3 ? fabsf(T[3]) - E[3] : fabsf(T[2]) - E[2]);
-        const float n1 = (deg == 3 ? fabsf(T[2]) + E[2] : fabsf(T[1]) + E[1]);
-        const float n2 = (deg == 3 ? fabsf(T[1]) + E[1] : fabsf(T[0]) + E[0]);
-        const float n3 = (deg == 3 ? fabsf(T[0]) + E[0] : 0.0f);
-        ok = ok && (deg == 1 || (n1 < 1e4f * lead && n2 < 1e8f * lead && n3 < 1e12f * lead));
+    // 3. quadratic branch (:138-149): |t1| < 1e4 |t2| and |t0| < 1e8 |t2| keep the reference's own root error (u64 times the
+    //    intermediates of the quadratic formula) far below EPS / 2
+    if (deg == 2) {
+        const float lead = fabsf(T[2]) - E[2];
+        ok = ok && fabsf(T[1]) + E[1] < 1e4f * lead && fabsf(T[0]) + E[0] < 1e8f * lead;
     }
     // 3b. cubic branch: the reference chooses between Cardano and the trigonometric formula by the sign of
     //    delta = q^3 + r^2 of the NORMALISED cubic (surface_impl.h:112-116).  Two roots that are close relative to the
@@ -245,6 +244,7 @@ RT_HD int cubic_verdict_tb(float T[4], const float B[4], float hi, bool want_hit
     //    of FP64 rounding — the reference may then return the far root and ignore a crossing that P really has, or the
     //    other way round.  Nothing can be predicted there, so a verdict needs the sign of delta CERTIFIED in FP32:
     //    |delta| > 2 e_delta + 1e-12 (Qs^3 + Rs^2), with first-order error propagation through a_i = T_i / T_3.
+    float eroot = 1e-9f;   // bound of |reference's computed root - exact root of its polynomial|; degree <= 2: see 3.
     if (deg == 3) {
         const float inv = RT_CF_DIV(1.0f, T[3]);            // a few ulps: covered by the 4 u terms below
         const float x3 = E[3] * fabsf(inv);                 // relative error of T3; 1 / (1 - x) <= 1 + 1.34 x for x <= 1/4
@@ -268,15 +268,55 @@ RT_HD int cubic_verdict_tb(float T[4], const float B[4], float hi, bool want_hit
         const float Q = fabsf(q) + eq, R = fabsf(r) + er;
         const float ed = fmaf(3.0f * Q * Q, eq, fmaf(2.0f * R, er, 8.0f * RT_CF_U * scale));
         ok = ok && x3 < 0.25f && fabsf(delta) > fmaf(2.0f, ed, 1e-12f * scale) && scale < 1e37f;
+        // 3c. how far the reference's computed root can be from the exact root of its own cubic (KU = 32 u64):
+        //   Cardano: t = cbrt(r + sd) + cbrt(r - sd) - a2/3, sd = sqrt(delta).  r +- sd carry an absolute error
+        //     dx = KU (rs + scale / sd); the smaller one, xm = |q|^3 / (|r| + sd), suffers cancellation when q is small,
+        //     and cbrt amplifies by 1 / (3 x^(2/3)) — or, when dx is not small against xm, by nothing better than
+        //     2 cbrt(xm + dx).
+        //   trigonometric: t = c cos(theta + 2 k pi / 3) - a2/3, c = 2 sqrt(-q), theta = acos(v) / 3, v = r / sqrt(-q^3):
+        //     dv = KU (rs / |q|^1.5 + 2 qs / |q|), dtheta = 2 dv / (3 sqrt(1 - v^2)), 1 - v^2 = |delta| / |q|^3
+        //     (first order; required: dv < (1 - v^2) / 4).
+        //   Both plus KU times the magnitudes added up.  The bound becomes the slack of the interval ends (4.); a
+        //   verdict needs it below 1e-3.
+        const float KU = 32.0f * 1.1102230e-16f;
+        const float aq = fabsf(q), ar = fabsf(r), a2third = fabsf(a2) * (1.0f / 3.0f);
+        const float sd = cf_sqrt(fabsf(delta));
+        if (delta > 0.0f) {
+            const float xM = ar + sd;
+            const float xm = RT_CF_DIV(aq * aq * aq, xM);
+            const float dx = KU * (rs + RT_CF_DIV(scale, sd));
+            const float cM = cf_cbrt(xM);
+            const float eS = RT_CF_DIV(dx, 3.0f * cM * cM);
+            float eT, cm;
+            if (dx < 0.5f * xm) {
+                cm = cf_cbrt(0.5f * xm);
+                eT = RT_CF_DIV(dx, 3.0f * cm * cm);
+            }
+            else {
+                cm = cf_cbrt(xm + dx);
+                eT = 2.0f * cm;
+            }
+            eroot = 1.01f * (eS + eT) + KU * (cM + 1.3f * cm + a2third);
+        }
+        else {
+            const float sq = cf_sqrt(aq), c = 2.0f * sq, q15 = aq * sq;
+            const float dv = KU * (RT_CF_DIV(rs, q15) + 2.0f * RT_CF_DIV(qs, aq));
+            const float one_v2 = RT_CF_DIV(fabsf(delta), q15 * q15);
+            ok = ok && dv < 0.25f * one_v2;
+            eroot = 1.01f * c * RT_CF_DIV(2.0f * dv, 3.0f * cf_sqrt(one_v2)) + KU * (c + a2third);
+        }
+        ok = ok && eroot < 1e-3f;
     }
     // 4. sign-normalised lower polynomial g = s T - E <= s P
     const float s = T[0] > 0.0f ? 1.0f : -1.0f;
     // quadratic branch with t2 < 0 (:138-149) returns the LARGER root first: only a downward crossing proves a hit
     const bool hit_ok = want_hit && !(deg == 2 && T[2] < 0.0f && s < 0.0f);
     const float g0 = s * T[0] - E[0], g1 = s * T[1] - E[1], g2 = s * T[2] - E[2], g3 = s * T[3] - E[3];
-    const float e2 = 2e-7f;   // 2 EPS
-    // uniform lower bound of g over [EPS/2, 2 EPS]
-    const float la = g0 - 1.01f * (fabsf(g1) * e2 + fabsf(g2) * e2 * e2 + fabsf(g3) * e2 * e2 * e2) - 4.0f * RT_CF_U * fabsf(g0);
+    // uniform lower bound of s P over |t| <= tau, tau = EPS + eroot (at least 2 EPS): no root of P within eroot of EPS on
+    // either side — valid for negative t too, hence with |T_i| + E_i
+    const float e2 = fmaxf(2e-7f, 1.01f * (1e-7f + eroot));
+    const float la = g0 - 1.01f * e2 * fmaf(fmaf(fabsf(T[3]) + E[3], e2, fabsf(T[2]) + E[2]), e2, fabsf(T[1]) + E[1]) -
+                     4.0f * RT_CF_U * fabsf(g0);
     ok = ok && la > 0.0f;
     // critical points of g: 3 g3 x^2 + 2 g2 x + g1 = 0 (degree 3), 2 g2 x + g1 = 0 (degree 2)
     float x1 = -1.0f, x2 = -1.0f;   // "not in range"
@@ -296,9 +336,9 @@ RT_HD int cubic_verdict_tb(float T[4], const float B[4], float hi, bool want_hit
         ok = ok && fabsf(x1) < 3e38f && fabsf(x2) < 3e38f;
     }
     if (!ok) return RT_CF_UNK(1);
-    const float b_hi = hi * (1.0f + 2e-6f), b_lo = hi * (1.0f - 2e-6f);
+    const float b_hi = fmaf(hi, 1.0f + 2e-6f, eroot), b_lo = fmaf(hi, 1.0f - 2e-6f, -eroot);
     // bounds over [b_lo, b_hi]: sample at hi, widened by the variation over the range
-    const float var = 2.1e-6f * hi * fmaf(fmaf(3.0f * (fabsf(T[3]) + E[3]), hi, 2.0f * (fabsf(T[2]) + E[2])), hi, fabsf(T[1]) + E[1]);
+    const float var = fmaf(2.1e-6f, hi, 1.01f * eroot) * fmaf(fmaf(3.0f * (fabsf(T[3]) + E[3]), hi, 2.0f * (fabsf(T[2]) + E[2])), hi, fabsf(T[1]) + E[1]);
     const CfSample sb = cf_sample(s, T, E, hi);
     const bool in1 = x1 > e2 && x1 < b_hi, in2 = x2 > e2 && x2 < b_hi;
     const CfSample s1 = cf_sample(s, T, E, in1 ? x1 : hi);   // out-of-range points re-sample hi: no effect
