@@ -59,7 +59,10 @@ __device__ __forceinline__ RayF make_rayf(const d3 &o, const d3 &d, float center
     r.kc1 = 2.0f * (2.0f * e1 / S + 5.0f * RT_U32F);
     r.kc0 = 2.0f * (2.0f * e1 * S + 3.0f * e1 * e1 + 2.0f * RT_U32F * r2_max);
     // q2 <= 3 (omax + Cmax)^2 and A q2 must stay finite in FP32 (max 3.4e38): keep every factor below 1e9
-    r.safe = omax < 1e9f && center_max < 1e9f && r.A < 1e18f && r2_max < 1e18f;
+    // ... and the reference must really be in its quadratic branch: t2 = d.d > 1e-7 (surface_impl.h:138); a direction
+    // shorter than that (a point light within 0.3 mm of the hit) sends it to the linear formula, which the geometry
+    // above says nothing about
+    r.safe = omax < 1e9f && center_max < 1e9f && r.A < 1e18f && r2_max < 1e18f && r.A > 2e-7f;
     return r;
 }
 

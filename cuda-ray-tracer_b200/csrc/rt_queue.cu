@@ -326,7 +326,7 @@ render_queue_kernel(const __grid_constant__ SceneView g, const __grid_constant__
                     if (mode == M_TILE) {
                         pr.ex = (float) qd.x; pr.ey = (float) qd.y; pr.ez = (float) qd.z;
                         pr.A = fmaf(pr.ex, pr.ex, fmaf(pr.ey, pr.ey, pr.ez * pr.ez));
-                        if (cfg.tables_safe && cfg.primary_safe && pr.A < 1e18f) thr = 0.0f;
+                        if (cfg.tables_safe && cfg.primary_safe && pr.A < 1e18f && pr.A > 2e-7f) thr = 0.0f;
                     }
                     else {
                         pr.ex = (float) (qo.x - qs.light[it].px);
@@ -336,7 +336,7 @@ render_queue_kernel(const __grid_constant__ SceneView g, const __grid_constant__
                         const float De = sqrtf(pr.A) * 1.0001f;
                         const float eps = 0.010001f + 4.0f * RT_U32F * (De + 0.02f);
                         const float kappa = pr.A * 1.0002f * (2.0f * cfg.r_max * eps + eps * eps);
-                        if (cfg.tables_safe && pr.A < 1e18f) thr = -kappa;
+                        if (cfg.tables_safe && pr.A < 1e18f && pr.A > 2e-7f) thr = -kappa;   // > 2e-7: the reference is in its quadratic branch
                     }
                 }
                 else if (kind == FK_DIRECTION) {

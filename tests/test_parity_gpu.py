@@ -174,6 +174,17 @@ def test_edge_cases(pkg, rt, oracle, kernel):
                            obj(S.surface_sphere([-3, 1, 9], 1.5), 0.2)], dtype=S.OBJECT_DTYPE)
     sc.lights = lights
     check(sc, poses=("identity", "pose_a", "pose_b"))
+    # point lights sitting (almost) on the surface at the central pixel's hit point (0, 0, 6): the float-rounded shadow
+    # direction is shorter than sqrt(1e-7), so the reference's intersect_ray leaves its quadratic branch
+    # (surface_impl.h:138) and the FP32 sphere filter, which reasons about the quadratic, must stand aside
+    sc = S.Scene(65, 49, np.radians(0.05), bg, 2)
+    sc.objects = np.array([obj(S.surface_sphere([0, 0, 8], 2.0), 0.2), obj(S.surface_sphere([0.0003, 0, 6.5], 0.4999), 0.0, (0.2, 0.9, 0.3)),
+                           obj(S.surface_sphere([0, 0.5, 6.2], 0.5376), 0.0, (0.2, 0.3, 0.9))] +
+                          [obj(S.surface_sphere([4 + i, 3, 9], 0.5)) for i in range(8)], dtype=S.OBJECT_DTYPE)
+    sc.lights = np.array([S.light_spherical(1e-4, [1e-5, 0, 6.0001], [1, 1, 1]), S.light_spherical(1e-4, [0, 2e-5, 5.9999], [1, 0.5, 1]),
+                          S.light_spherical(1e-4, [-1e-4, 1e-4, 6.0002], [0.5, 1, 1]), S.light_spherical(30.0, [0, 1.0, 5.5], [1, 1, 0.5])],
+                         dtype=S.LIGHT_DTYPE)
+    check(sc, poses=("identity",))
 
 
 @pytest.mark.parametrize("kernel", KERNELS)
