@@ -231,6 +231,7 @@ def run_b200(args):
     for label, sc in scenes:
         r = binding.Renderer(sc, device=local, rank=rank, world_size=world)
         r.set_option("kernel", args.kernel)
+        r.set_option("accel", args.accel)
         if world > 1:
             r.set_option("strip_rows", args.strip_rows)
             ident = [binding.comm_unique_id() if rank == 0 else None]
@@ -276,9 +277,11 @@ def run_b200(args):
     for label, _, r in renderers:
         r.set_option("count", 1)
         r.set_option("cull_backfacing", 0)
+        r.set_option("accel", 0)        # the census is the reference's brute-force loops, whatever the timed mode is
         r.update(m)
         local_counts[label] = r.counters()
         r.set_option("cull_backfacing", 1 if args.cull else 0)
+        r.set_option("accel", args.accel)
         r.update(m)
         traced_counts[label] = r.counters()
         r.set_option("count", 0)        # counters are instrumentation, not part of the frame: off while timing
@@ -370,6 +373,10 @@ def run_b200(args):
                        "rays_per_step": rays_step, "rays_traced_per_step": rays_traced,
                        "ray_count": "rays_per_step = rays the reference casts (metric); rays_traced_per_step = rays this kernel "
                                     "traces: shadow rays towards lights with Lambert factor 0 at the hit add exactly 0 and are skipped", "kernel": args.kernel,
+                       "accel": {"mode": args.accel, "sphere_tests_examined_rank0": int(sum(c["tests_sphere"] for c in traced_counts.values())),
+                                 "what": "0 = brute force over all objects like the reference (the roofline is quoted on this); 1 = sphere "
+                                         "class through the uniform grid (SURVEY §8 f4): identical frames, canonical flops still those "
+                                         "of the brute-force census, so roofline.frac is reference-equivalent work and can exceed 1"},
                        "parallelism": "strips{}x{}rows,{}".format(world, args.strip_rows, "p2p-store+flags" if fused else
                                                                   "nccl-allgather") if world > 1 else "1gpu",
                        "timing": "CUDA events on the render stream per frame, summed; max over ranks",
@@ -447,6 +454,8 @@ def main():
     ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"], help="multi-GPU frame assembly")
     ap.add_argument("--e2e", default="shared", choices=["shared", "gather"], help="multi-GPU end-to-end leg: every rank "
                     "copies its strips into one shared host frame, or rank 0 gathers on the device and copies alone")
+    ap.add_argument("--accel", type=int, default=0, choices=[-1, 0, 1], help="sphere-class grid (separate mode, SURVEY §8 f4): "
+                    "0 = brute force like the reference (default, what the roofline is quoted on), 1 = on, -1 = library default")
     ap.add_argument("--no-cull", dest="cull", action="store_false", help="trace every shadow ray the reference casts")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

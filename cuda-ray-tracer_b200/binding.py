@@ -28,7 +28,8 @@ EXPORTS = ("rt_b200_upload_scene", "rt_b200_update", "rt_b200_gather", "rt_b200_
            "rt_b200_comm_unique_id", "rt_b200_comm_init", "rt_b200_get_counters", "rt_b200_set_option",
            "rt_b200_get_timing", "rt_b200_get_class_counts", "rt_b200_strip_layout", "rt_b200_version",
            "rt_b200_update_to_host", "rt_b200_frame_export", "rt_b200_frame_attach", "rt_b200_get_launches",
-           "rt_b200_host_alloc", "rt_b200_host_free", "rt_b200_host_alloc_shared", "rt_b200_host_free_shared")
+           "rt_b200_host_alloc", "rt_b200_host_free", "rt_b200_host_alloc_shared", "rt_b200_host_free_shared",
+           "rt_b200_get_grid_info")
 
 UNIQUE_ID_BYTES = 128
 IPC_HANDLE_BYTES = 64
@@ -66,6 +67,7 @@ def load_library():
     L.rt_b200_set_option.argtypes = [vp, C.c_char_p, C.c_int64]
     L.rt_b200_get_timing.argtypes = [vp, C.POINTER(C.c_float * 2)]
     L.rt_b200_get_class_counts.argtypes = [vp, C.POINTER(C.c_uint32 * 4)]
+    L.rt_b200_get_grid_info.argtypes = [vp, C.POINTER(C.c_uint32 * 6)]
     L.rt_b200_version.restype = C.c_char_p
     L.rt_b200_update_to_host.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(C.c_float)]
     L.rt_b200_frame_export.argtypes = [vp, vp]
@@ -221,6 +223,12 @@ class Renderer:
         t = (C.c_uint32 * 4)()
         _check(load_library().rt_b200_get_class_counts(self._h, C.byref(t)))
         return {"plane": t[0], "sphere": t[1], "quadric": t[2], "cubic": t[3]}
+
+    def grid_info(self):
+        """The sphere grid built at upload (option accel, csrc/rt_grid.cuh)."""
+        t = (C.c_uint32 * 6)()
+        _check(load_library().rt_b200_get_grid_info(self._h, C.byref(t)))
+        return {"nx": t[0], "ny": t[1], "nz": t[2], "gridded": t[3], "loose": t[4], "registrations": t[5]}
 
     # -- update.h:8
     def close(self):

@@ -29,6 +29,7 @@
 #include <vector>
 
 #include "../../include/rt_b200.h"
+#include "rt_grid_build.h"
 #include "rt_kernels.h"
 #include "rt_queue.cuh"
 
@@ -158,6 +159,7 @@ cudaError_t upload(const std::vector<T> &host, T **dev)
 } // namespace
 
 #define RT_MAX_BANDS 16
+#define RT_GRID_AUTO_SPHERES 64
 
 struct rt_b200_ctx {
     int device = 0, rank = 0, world = 1;
@@ -192,6 +194,12 @@ struct rt_b200_ctx {
     int wave_variant = 0;
     int cubic_filter = 1;
     int cull_backfacing = 1;
+    // sphere grid (rt_grid.cuh): built at upload; accel = -1 automatic (on from RT_GRID_AUTO_SPHERES
+    // sphere-class objects), 0 brute force, 1 on.  Frames are identical either way.
+    int accel = -1;
+    int *d_grid_cells = nullptr, *d_grid_items = nullptr;
+    std::vector<double> sphere_centres, sphere_r2;   // kept for rebuilding the grid at another density
+    uint32_t grid_info[6] = {0, 0, 0, 0, 0, 0};      // nx, ny, nz, gridded spheres, loose spheres, registrations
     bool sync_in_kernel = false;       // this frame's go / flag words are handled inside the wavefront kernel
     bool tile_counter_dirty = false;   // another kernel used the tile counter: zero it before the wavefront kernel
     double trace[5] = {0, 0, 0, 0, 0};   // RT_B200_TRACE=1: seconds spent per stage of update_to_host (shared block)
@@ -266,6 +274,33 @@ int ensure_buffers(rt_b200_ctx *c)
 }
 
 // Structural class of one object: which coefficients are exactly zero.
+// (Re)build the sphere grid at `density` cells per sphere (<= 0: the builder's default) and point the view at it.
+int build_grid(rt_b200_ctx *c, double density)
+{
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    cudaFree(c->d_grid_cells);
+    cudaFree(c->d_grid_items);
+    c->d_grid_cells = c->d_grid_items = nullptr;
+    c->view.grid = rt::SphereGrid{};
+    std::memset(c->grid_info, 0, sizeof(c->grid_info));
+    const int n = (int) c->sphere_r2.size();
+    if (n == 0) return RT_B200_OK;
+    rt::SphereGridHost H = rt::build_sphere_grid(c->sphere_centres.data(), c->sphere_r2.data(), n, density);
+    cudaError_t e = upload(H.cell_start, &c->d_grid_cells);
+    if (e == cudaSuccess) e = upload(H.items, &c->d_grid_items);
+    if (e != cudaSuccess) return fail(RT_B200_ERR_CUDA, "upload sphere grid: %s", cudaGetErrorString(e));
+    H.g.cell_start = c->d_grid_cells;
+    H.g.items = c->d_grid_items;
+    c->view.grid = H.g;
+    c->grid_info[0] = (uint32_t) H.g.n[0];
+    c->grid_info[1] = (uint32_t) H.g.n[1];
+    c->grid_info[2] = (uint32_t) H.g.n[2];
+    c->grid_info[3] = (uint32_t) H.g.n_gridded;
+    c->grid_info[4] = (uint32_t) (H.g.loose_end - H.g.loose_begin);
+    c->grid_info[5] = (uint32_t) H.g.loose_begin;
+    return RT_B200_OK;
+}
+
 rt::ObjClass classify(const double *k)
 {
     for (int i = rt::X3; i <= rt::XYZ; i++)
@@ -345,6 +380,8 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
                 double cx = -0.5 * k[rt::LX], cy = -0.5 * k[rt::LY], cz = -0.5 * k[rt::LZ];
                 double r2 = cx * cx + cy * cy + cz * cz - k[rt::CC];
                 sphere_f.push_back(make_float4((float) cx, (float) cy, (float) cz, (float) r2));
+                c->sphere_centres.insert(c->sphere_centres.end(), {cx, cy, cz});
+                c->sphere_r2.push_back(r2);
                 r2_max = fmaxf(r2_max, nextafterf((float) fabs(r2), INFINITY));
                 center_max = fmaxf(center_max, fmaxf(fabsf((float) cx), fmaxf(fabsf((float) cy), fabsf((float) cz))));
                 center_norm_max = fmaxf(center_norm_max, nextafterf((float) sqrt(cx * cx + cy * cy + cz * cz), INFINITY));
@@ -462,7 +499,8 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     v.lights = c->d_lights;
     v.sphere_center_max = center_max;
 
-    rc = ensure_buffers(c);
+    rc = build_grid(c, 0.0);
+    if (rc == RT_B200_OK) rc = ensure_buffers(c);
     if (rc == RT_B200_OK) {
         // light families and every table row that does not depend on the camera (rows 0 and 2..)
         const double zero[3] = {0.0, 0.0, 0.0};
@@ -509,7 +547,9 @@ int launch_kernel(rt_b200_ctx *c, const rt::FrameParams &f)
             c->tile_counter_dirty = false;
         }
         rt::WaveLaunch wl{c->d_tile_counter, c->d_cubic_mask, c->sphere_r2_max, c->shadow_cache, c->wave_variant, c->cubic_filter,
-                          (c->cull_backfacing && c->cull_safe) ? 1 : 0, nullptr, nullptr, nullptr, 0u};
+                          (c->cull_backfacing && c->cull_safe) ? 1 : 0,
+                          (c->accel > 0 || (c->accel < 0 && c->view.n_sphere >= RT_GRID_AUTO_SPHERES)) ? 1 : 0,
+                          nullptr, nullptr, nullptr, 0u};
         if (c->sync_in_kernel) {   // fused gather: the render kernel does the frame hand-shake itself
             wl.sync_go = c->d_go;
             wl.sync_flags = c->d_flags;
@@ -931,6 +971,8 @@ int rt_b200_destroy(rt_b200_ctx *c)
     cudaFree(c->d_counters);
     cudaFree(c->d_tile_counter);
     cudaFree(c->d_cubic_mask);
+    cudaFree(c->d_grid_cells);
+    cudaFree(c->d_grid_items);
     cudaFree(c->qtables.tables);
     delete c->qscene;
     if (c->ev_start) cudaEventDestroy(c->ev_start);
@@ -1020,6 +1062,14 @@ int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
     else if (!std::strcmp(name, "cubic_filter")) {
         c->cubic_filter = value ? 1 : 0;
     }
+    else if (!std::strcmp(name, "accel")) {
+        if (value < -1 || value > 1) return fail(RT_B200_ERR_ARG, "accel must be -1, 0 or 1");
+        c->accel = (int) value;
+    }
+    else if (!std::strcmp(name, "grid_density")) {   // cells per sphere x 100 (0 = default)
+        if (value < 0 || value > 100000) return fail(RT_B200_ERR_ARG, "grid_density must be 0..100000");
+        return build_grid(c, (double) value / 100.0);
+    }
     else if (!std::strcmp(name, "host_bands")) {
         if (value < 0 || value > RT_MAX_BANDS) return fail(RT_B200_ERR_ARG, "host_bands must be 0..%d", RT_MAX_BANDS);
         c->host_bands = (int) value;
@@ -1074,6 +1124,13 @@ int rt_b200_get_class_counts(rt_b200_ctx *c, uint32_t out[4])
 {
     if (!c || !out) return fail(RT_B200_ERR_ARG, "null argument");
     std::memcpy(out, c->class_counts, sizeof(c->class_counts));
+    return RT_B200_OK;
+}
+
+int rt_b200_get_grid_info(rt_b200_ctx *c, uint32_t out[6])
+{
+    if (!c || !out) return fail(RT_B200_ERR_ARG, "null argument");
+    std::memcpy(out, c->grid_info, sizeof(c->grid_info));
     return RT_B200_OK;
 }
 

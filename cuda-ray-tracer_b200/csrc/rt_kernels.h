@@ -18,6 +18,7 @@ struct WaveLaunch {
     int variant;                        // 0 = automatic; 2 / 3 = 256-thread CTAs, two / three per SM; 5 = one 512-thread CTA
     int cubic_filter;                   // 1 = FP32 filter in front of the exact cubic test (rt_cubic_filter.cuh)
     int cull_backfacing;                // 1 = no shadow ray towards a light whose Lambert factor is 0 at the hit
+    int accel;                          // 1 = sphere class through the uniform grid (SceneView::grid), 0 = brute force
     // fused multi-GPU gather: sequence words in rank 0's memory (go == nullptr: none), see WaveSync in rt_wave.cuh
     unsigned *sync_go, *sync_flags, *sync_timed_out;
     unsigned sync_seq;

@@ -19,6 +19,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "rt_grid.cuh"
+
 namespace rt {
 
 enum ObjClass { CLS_PLANE = 0, CLS_SPHERE = 1, CLS_QUADRIC = 2, CLS_CUBIC = 3 };
@@ -45,6 +47,7 @@ struct SceneView {
     const float4 *material;   // [n_objects] by ORIGINAL index {reflection_ratio, r, g, b}
     const LightDev *lights;   // [n_lights]
     float sphere_center_max;  // max |coordinate| over all sphere centres (FP32 filter error bound)
+    SphereGrid grid;          // uniform grid over the sphere class (rt_grid.cuh); cell_start == nullptr: none
 };
 
 // Work counters, one 64-bit slot each; order matches rt_b200_counters in include/rt_b200.h.

@@ -76,6 +76,7 @@ struct WaveConfig {
     int spheres_in_smem;
     int use_shadow_cache;
     int use_cubic_filter;
+    int use_grid;                // sphere class through the uniform grid (rt_grid.cuh) instead of the brute-force loop
     int cull_backfacing;         // skip shadow rays of lights whose Lambert factor is 0 at the hit (they add exactly 0)
     unsigned long long *tile_counter;   // [0] next tile, [1] CTAs finished; the last CTA leaves both at 0
     WaveSync sync;

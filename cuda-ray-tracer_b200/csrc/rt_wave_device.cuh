@@ -10,9 +10,85 @@ namespace rt {
 
 namespace {
 
+// ---- sphere class through the uniform grid (rt_grid.cuh; option accel) -----------------------------------
+// The grid only proposes candidates: each one goes through the same FP32 filter and exact FP64 test as in the
+// brute-force loops below, so the frame is identical.  Out of line on purpose: the walker's registers must not
+// weigh on the scenes that never call it.
+struct GridNearestResult {
+    double t;
+    int slot;            // class-sorted slot, -1 = none so far
+    unsigned confirms, tests;
+};
+
+struct GridNearestVisitor {
+    const SceneView &g;
+    const RayF &rf;
+    const d3 &o, &d;
+    GridNearestResult r;
+    __device__ __forceinline__ bool test(int j)
+    {
+        r.tests++;
+        if (!rf.safe || !sphere_rejected<false>(rf, __ldg(&g.sphere_f[j]))) {
+            r.confirms++;
+            consider_lazy_t(r.t, r.slot, intersect_sphere(g.sphere[j], o, d), g.n_plane + j, g.orig_index);
+        }
+        return false;
+    }
+    __device__ __forceinline__ double bound() const { return r.t; }
+};
+
+template <bool SEGMENT01>
+struct GridOccluderVisitor {
+    const SceneView &g;
+    const RayF &rf;
+    const d3 &o, &d;
+    double max_t;
+    int found;
+    unsigned confirms, tests;
+    __device__ __forceinline__ bool test(int j)
+    {
+        tests++;
+        if (!rf.safe || !sphere_rejected<SEGMENT01>(rf, __ldg(&g.sphere_f[j]))) {
+            confirms++;
+            if (blocks(intersect_sphere(g.sphere[j], o, d), max_t)) {
+                found = g.n_plane + j;
+                return true;
+            }
+        }
+        return false;
+    }
+    __device__ __forceinline__ double bound() const { return max_t; }
+};
+
+// best_t / best_slot: the nearest hit found so far among the classes visited earlier (it bounds the walk)
+static __device__ __noinline__ GridNearestResult nearest_spheres_grid(const SceneView &g, float sphere_r2_max, d3 o, d3 d,
+                                                                      double best_t, int best_slot)
+{
+    const RayF rf = make_rayf(o, d, g.sphere_center_max, sphere_r2_max);
+    GridNearestVisitor v{g, rf, o, d, GridNearestResult{best_t, best_slot, 0u, 0u}};
+    grid_walk(g.grid, o.x, o.y, o.z, d.x, d.y, d.z, RT_MAX_T, v);
+    return v.r;
+}
+
+struct GridOccluderResult {
+    int found;           // occluding slot or -1
+    unsigned confirms, tests;
+};
+
+template <bool SEGMENT01>
+static __device__ __noinline__ GridOccluderResult occluder_spheres_grid(const SceneView &g, float sphere_r2_max, d3 o, d3 d,
+                                                                        double max_t)
+{
+    const RayF rf = make_rayf(o, d, g.sphere_center_max, sphere_r2_max);
+    GridOccluderVisitor<SEGMENT01> v{g, rf, o, d, max_t, -1, 0u, 0u};
+    grid_walk(g.grid, o.x, o.y, o.z, d.x, d.y, d.z, max_t, v);
+    return GridOccluderResult{v.found, v.confirms, v.tests};
+}
+
 // ---- phase A: nearest hit (update-cpu.cpp:48-56) ---------------------------------------------------------
 // CUBIC = false compiles the cubic class out (scenes without cubics run a leaner kernel).
-template <bool CUBIC>
+// GRID = true compiles the grid walk in (its own kernel instantiations, so the brute-force kernels carry none of it).
+template <bool CUBIC, bool GRID>
 __device__ __forceinline__ Hit nearest_hit_wave(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg,
                                                 const d3 &o, const d3 &d, bool primary, bool filter, Tally &tl)
 {
@@ -22,7 +98,15 @@ __device__ __forceinline__ Hit nearest_hit_wave(const SceneView &g, const SceneS
     h.orig = 0x7fffffff;
     int slot = 0;
     for (int i = 0; i < g.n_plane; i++, slot++) consider_lazy(h, intersect_plane(s.plane[i], o, d), slot, g.orig_index);
-    if (g.n_sphere > 0) {
+    if (GRID && g.n_sphere > 0 && cfg.use_grid && grid_ray_ok(g.grid, o.x, o.y, o.z, d.x, d.y, d.z)) {
+        const GridNearestResult r = nearest_spheres_grid(g, cfg.sphere_r2_max, o, d, h.t, h.slot);
+        h.t = r.t;
+        h.slot = r.slot;
+        slot += g.n_sphere;
+        tl.n[CNT_CONFIRM] += r.confirms;
+        tl.n[CNT_T_SPHERE] += r.tests;
+    }
+    else if (g.n_sphere > 0) {
         const RayF rf = make_rayf(o, d, g.sphere_center_max, cfg.sphere_r2_max);
         unsigned confirms = 0;
         const int n4 = rf.safe ? (g.n_sphere & ~3) : 0;
@@ -49,6 +133,7 @@ __device__ __forceinline__ Hit nearest_hit_wave(const SceneView &g, const SceneS
         }
         slot += g.n_sphere;
         tl.n[CNT_CONFIRM] += confirms;
+        tl.n[CNT_T_SPHERE] += g.n_sphere;
     }
     for (int i = 0; i < g.n_quadric; i++, slot++)
         consider_lazy(h, intersect_quadric(s.quadric + 10 * i, o, d), slot, g.orig_index);
@@ -73,7 +158,6 @@ __device__ __forceinline__ Hit nearest_hit_wave(const SceneView &g, const SceneS
     }
     if (h.slot >= 0) h.orig = __ldg(&g.orig_index[h.slot]);
     tl.n[CNT_T_PLANE] += g.n_plane;
-    tl.n[CNT_T_SPHERE] += g.n_sphere;
     tl.n[CNT_T_QUADRIC] += g.n_quadric;
     if (CUBIC) tl.n[CNT_T_CUBIC] += g.n_cubic;
     return h;
@@ -110,10 +194,16 @@ __device__ __forceinline__ double intersect_slot(const SceneView &g, const Scene
 // The boolean is order-independent, so classes are visited cheapest-first, except that the cubic class moves
 // in front of the sphere class while cubics are the more productive occluders per unit of work (block-local
 // statistics in WaveCtl::occ_found, updated as occluders are found).
-template <bool SEGMENT01>
+template <bool SEGMENT01, bool GRID>
 __device__ __forceinline__ int occluder_spheres(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg,
                                                 const d3 &o, const d3 &d, double max_t, Tally &tl)
 {
+    if (GRID && cfg.use_grid && grid_ray_ok(g.grid, o.x, o.y, o.z, d.x, d.y, d.z)) {
+        const GridOccluderResult r = occluder_spheres_grid<SEGMENT01>(g, cfg.sphere_r2_max, o, d, max_t);
+        tl.n[CNT_T_SPHERE] += r.tests;
+        tl.n[CNT_CONFIRM] += r.confirms;
+        return r.found;
+    }
     const int slot = g.n_plane;
     const RayF rf = make_rayf(o, d, g.sphere_center_max, cfg.sphere_r2_max);
     int found = -1;
@@ -178,7 +268,7 @@ __device__ __forceinline__ int occluder_cubics(const SceneView &g, const SceneSm
     return -1;
 }
 
-template <bool SEGMENT01, bool CUBIC>
+template <bool SEGMENT01, bool CUBIC, bool GRID>
 __device__ __forceinline__ int occluder_wave(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg, WaveCtl &ctl,
                                              const d3 &o, const d3 &d, double max_t, int hit_slot, int light, Tally &tl)
 {
@@ -192,16 +282,18 @@ __device__ __forceinline__ int occluder_wave(const SceneView &g, const SceneSmem
         if (blocks(intersect_quadric(s.quadric + 10 * i, o, d), max_t)) return quad_base + i;
     }
     if (g.n_sphere == 0) return (CUBIC && g.n_cubic) ? occluder_cubics(g, s, cfg, o, d, max_t, hit_slot, light, tl) : -1;
-    if (!CUBIC || g.n_cubic == 0) return occluder_spheres<SEGMENT01>(g, s, cfg, o, d, max_t, tl);
-    // relative cost of a full pass: ~4 issue slots x 4 per sphere filter, ~600 per exact cubic test
+    if (!CUBIC || g.n_cubic == 0) return occluder_spheres<SEGMENT01, GRID>(g, s, cfg, o, d, max_t, tl);
+    // relative cost of a full pass: ~4 issue slots x 4 per sphere filter (a flat ~2000 for a grid walk), ~600 per exact
+    // cubic test
     const volatile int *found = ctl.occ_found;
-    const bool cubic_first = (long long) found[1] * (16LL * g.n_sphere) > (long long) found[0] * (600LL * g.n_cubic);
-    int by = cubic_first ? occluder_cubics(g, s, cfg, o, d, max_t, hit_slot, light, tl) : occluder_spheres<SEGMENT01>(g, s, cfg, o, d, max_t, tl);
+    const long long sphere_pass = (GRID && cfg.use_grid) ? 2000LL : 16LL * g.n_sphere;
+    const bool cubic_first = (long long) found[1] * sphere_pass > (long long) found[0] * (600LL * g.n_cubic);
+    int by = cubic_first ? occluder_cubics(g, s, cfg, o, d, max_t, hit_slot, light, tl) : occluder_spheres<SEGMENT01, GRID>(g, s, cfg, o, d, max_t, tl);
     if (by >= 0) {
         atomicAdd(&ctl.occ_found[cubic_first ? 1 : 0], 1);
         return by;
     }
-    by = cubic_first ? occluder_spheres<SEGMENT01>(g, s, cfg, o, d, max_t, tl) : occluder_cubics(g, s, cfg, o, d, max_t, hit_slot, light, tl);
+    by = cubic_first ? occluder_spheres<SEGMENT01, GRID>(g, s, cfg, o, d, max_t, tl) : occluder_cubics(g, s, cfg, o, d, max_t, hit_slot, light, tl);
     if (by >= 0) atomicAdd(&ctl.occ_found[cubic_first ? 0 : 1], 1);
     return by;
 }

@@ -26,7 +26,7 @@ __device__ __forceinline__ float blend(float out, float ratio, float c) { return
 
 } // namespace
 
-template <int W, int MINB, bool COUNT, bool CUBIC>
+template <int W, int MINB, bool COUNT, bool CUBIC, bool GRID>
 __global__ void __launch_bounds__(W, MINB)
 render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ FrameParams f,
                    const __grid_constant__ WaveConfig cfg)
@@ -210,7 +210,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         // ---- phase A + B: nearest hit, hit record, compact hit list ---------------------------------------
         int obj = -1;
         if (active) {
-            Hit h = nearest_hit_wave<CUBIC>(g, s, cfg, o, d, primary, !primary || prim_filter, tl);
+            Hit h = nearest_hit_wave<CUBIC, GRID>(g, s, cfg, o, d, primary, !primary || prim_filter, tl);
             if (h.slot >= 0) {
                 obj = h.orig;
                 const d3 p = d3{o.x + h.t * d.x, o.y + h.t * d.y, o.z + h.t * d.z};
@@ -301,8 +301,8 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
                             if (cs >= 0) occ = blocks(intersect_slot<CUBIC>(g, s, cs, so, sd, tl), max_t);
                         }
                         if (!occ) {
-                            const int by = l.is_spherical ? occluder_wave<true, CUBIC>(g, s, cfg, ctl, so, sd, max_t, k, l0 + j, tl)
-                                                          : occluder_wave<false, CUBIC>(g, s, cfg, ctl, so, sd, max_t, k, l0 + j, tl);
+                            const int by = l.is_spherical ? occluder_wave<true, CUBIC, GRID>(g, s, cfg, ctl, so, sd, max_t, k, l0 + j, tl)
+                                                          : occluder_wave<false, CUBIC, GRID>(g, s, cfg, ctl, so, sd, max_t, k, l0 + j, tl);
                             occ = by >= 0;
                             if (occ && cfg.use_shadow_cache) ctl.shadow_cache[j] = by;   // benign race: any occluder will do
                         }
@@ -416,16 +416,16 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
 
 namespace {
 
-template <int W, int MINB, bool CUBIC>
+template <int W, int MINB, bool CUBIC, bool GRID = false>
 cudaError_t launch_wave_variant(const SceneView &scene, const FrameParams &frame, WaveConfig cfg, size_t scene_smem,
                                 int n_sm, int max_smem, cudaStream_t stream)
 {
     static bool attr_set = false;
-    auto kern = frame.counters ? render_wave_kernel<W, MINB, true, CUBIC> : render_wave_kernel<W, MINB, false, CUBIC>;
+    auto kern = frame.counters ? render_wave_kernel<W, MINB, true, CUBIC, GRID> : render_wave_kernel<W, MINB, false, CUBIC, GRID>;
     cudaError_t e;
     if (!attr_set) {
-        e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, true, CUBIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, false, CUBIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, true, CUBIC, GRID>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, false, CUBIC, GRID>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
@@ -466,14 +466,23 @@ cudaError_t launch_render_wave_t(const SceneView &scene, const FrameParams &fram
     cfg.use_shadow_cache = wl.shadow_cache >= 0 ? wl.shadow_cache : (scene.n_objects >= 8 ? 1 : 0);
     cfg.use_cubic_filter = wl.cubic_filter;
     cfg.cull_backfacing = wl.cull_backfacing;
-    cfg.spheres_in_smem = 1;
-    size_t scene_smem = wave_scene_smem(scene, true);
-    if (wave_fixed_smem<512>() + scene_smem + wave_cubic_smem(scene, 512) > (size_t) max_smem) {
+    // with the grid the FP32 sphere array is read a few candidates at a time (L1/L2): it is not staged, which leaves
+    // room for three CTAs per SM; rays the walker refuses (rt_grid.cuh: grid_ray_ok) run the brute-force loop from L2
+    cfg.use_grid = (wl.accel && scene.grid.cell_start != nullptr && scene.n_sphere > 0) ? 1 : 0;
+    cfg.spheres_in_smem = cfg.use_grid ? 0 : 1;
+    size_t scene_smem = wave_scene_smem(scene, cfg.spheres_in_smem != 0);
+    if (cfg.spheres_in_smem && wave_fixed_smem<512>() + scene_smem + wave_cubic_smem(scene, 512) > (size_t) max_smem) {
         cfg.spheres_in_smem = 0;
         scene_smem = wave_scene_smem(scene, false);
-        if (wave_fixed_smem<256>() + scene_smem + wave_cubic_smem(scene, 256) > (size_t) max_smem) return cudaErrorInvalidConfiguration;
     }
+    if (!cfg.spheres_in_smem && wave_fixed_smem<256>() + scene_smem + wave_cubic_smem(scene, 256) > (size_t) max_smem)
+        return cudaErrorInvalidConfiguration;
     const size_t cta256 = wave_fixed_smem<256>() + scene_smem + wave_cubic_smem(scene, 256) + 1024;   // + per-CTA reservation
+    // the grid walk is compiled into the 256-thread variants only (nothing is staged for the spheres, so three CTAs fit)
+    if (cfg.use_grid) {
+        if (wl.variant == 2) return launch_wave_variant<256, 2, CUBIC, true>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
+        return launch_wave_variant<256, 3, CUBIC, true>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
+    }
     int variant = wl.variant;
     if (variant <= 0) variant = (3 * cta256 <= (size_t) sm_smem) ? 3 : 5;
     switch (variant) {

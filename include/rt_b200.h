@@ -148,7 +148,14 @@ int rt_b200_get_counters(rt_b200_ctx *ctx, rt_b200_counters *out);
  *          "cull_backfacing" 1 (default, kernel 1): no shadow ray is traced towards a light whose Lambert factor
  *                       max(0, n.dir) is 0 at the hit — such a light adds exactly 0 whether occluded or not, so
  *                       frames are identical; rt_b200_counters then report the rays actually traced.  0 = trace every
- *                       shadow ray the reference casts (the counters equal the reference's ray census)            */
+ *                       shadow ray the reference casts (the counters equal the reference's ray census)
+ *           "accel"     sphere-class acceleration (wavefront kernel): 1 = rays look only at the
+ *                       spheres registered in the uniform-grid cells they pass (csrc/rt_grid.cuh), each candidate still
+ *                       going through the exact test, so frames are identical to the brute-force loops of
+ *                       update-cpu.cpp:48-56,66-72; 0 = brute force (what the roofline figures are quoted on);
+ *                       -1 (default) = on for scenes with at least 64 sphere-class objects.  With the grid on, the
+ *                       tests_sphere / confirms counters report the candidates actually examined
+ *           "grid_density"  rebuild the grid at value / 100 cells per sphere (0 = default 1.5)                      */
 int rt_b200_set_option(rt_b200_ctx *ctx, const char *name, int64_t value);
 
 /* Split timing of the last update, milliseconds: [0] render kernels, [1] gather (all-gather + unpack). */
@@ -159,6 +166,10 @@ int rt_b200_get_launches(rt_b200_ctx *ctx, uint32_t *launches);
 
 /* Structural class counts of the uploaded scene: planes, spheres, quadrics, cubics. */
 int rt_b200_get_class_counts(rt_b200_ctx *ctx, uint32_t out[4]);
+
+/* The sphere grid built at upload (option "accel"): cells along x, y, z; spheres registered in cells; spheres kept on
+ * the always-tested list (too large, too small or non-finite for the grid); cell registrations in total. */
+int rt_b200_get_grid_info(rt_b200_ctx *ctx, uint32_t out[6]);
 
 /* Host-only helper (needs no GPU): the strip interleave of the multi-GPU split.  Rank r of world_size owns
  * the strips s (of strip_rows image rows each) with s % world_size == r and stores them packed, padded to

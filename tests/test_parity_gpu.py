@@ -354,3 +354,87 @@ def test_cubic_filter_and_culling_paths(pkg, rt, oracle):
                 assert seen[(1, 0)]["cubic_exact"] <= seen[(0, 0)]["cubic_exact"]
                 assert seen[(1, 1)]["shadow_rays"] <= seen[(1, 0)]["shadow_rays"]
                 assert seen[(0, 0)]["shadow_rays"] == seen[(0, 0)]["hits"] * len(ls)
+
+
+def test_sphere_grid_frames_identical(pkg, rt, oracle, scenes_dir):
+    """Option accel (csrc/rt_grid.cuh): with the sphere class walked through the uniform grid the frame
+    is byte-identical to the brute-force loops (wavefront kernel with accel = 0, and the exact kernel), at every grid
+    density and in both kernel variants; the ray census is unchanged and far fewer spheres are examined."""
+    from cuda_ray_tracer_b200 import camera, synth
+    from cuda_ray_tracer_b200 import scene as S
+    bg = np.array([0.2, 0.3, 0.4], dtype=np.float32)
+    rng = np.random.default_rng(11)
+    obj = lambda k, refl=0.0, col=(0.8, 0.6, 0.2): S.make_object(k, refl, col)
+
+    def cloud(n, scale, extras):
+        objs = []
+        for i in range(n):
+            c = rng.uniform(-1, 1, 3) * scale * np.array([1.0, 0.6, 1.0]) + np.array([0, 0, 2.2 * scale])
+            objs.append(obj(S.surface_sphere(list(c), float(rng.uniform(0.02, 0.09) * scale)), 0.3 if i % 4 == 0 else 0.0,
+                            tuple(rng.uniform(0.1, 0.9, 3))))
+        return objs + extras
+
+    far_pose = camera.camera_matrix((3.0e5, 2.0, -5.0), 80.0, -10.0)      # the walker refuses such origins: brute force
+    lights = np.array([S.light_spherical(3000.0, [3, 9, 14], [1, 0.9, 0.8]), S.light_spherical(2000.0, [-6, -2, 25], [0.8, 0.9, 1]),
+                       S.light_directional(1.5, [0.3, -1, 0.5], [1, 1, 1])], dtype=S.LIGHT_DTYPE)
+    dup = S.surface_sphere([0.5, 0.25, 20.0], 1.5)
+    cases = {}
+    sc = synth.synthetic_scene(n_spheres=600, n_cubics=3, n_lights=4, width=192, height=108)
+    cases["synthetic 600 spheres + 3 cubics"] = (sc, ("identity", "pose_a"))
+    sc = S.Scene(160, 100, np.radians(60.0), bg, 4)
+    sc.objects = np.array(cloud(300, 10.0, [
+        obj(dup, 0.0, (0.9, 0.1, 0.1)), obj(dup, 0.5, (0.1, 0.9, 0.1)),                  # exact tie: lowest index wins
+        obj(S.surface_sphere([0.5, 0.25, 20.0], 0.7), 0.0),                              # nested
+        obj(S.surface_sphere([0, 0, 22.0], 400.0), 0.0, (0.3, 0.3, 0.5)),                # huge, contains the camera: loose
+        obj(S.surface_sphere([1, 1, 15.0], 1e-6), 0.0),                                  # tiny: loose
+        obj(S.surface_sphere([500.0, 0, 22.0], 3.0), 0.0),                               # outlier stretching the bounds
+        obj(S.surface_plane([0, -7, 0], [0, 1, 0]), 0.4, (0.5, 0.5, 0.5))]), dtype=S.OBJECT_DTYPE)
+    sc.lights = lights
+    cases["random cloud with awkward spheres + mirror plane"] = (sc, ("identity", "pose_b", far_pose))
+    cases["20spheres (grid forced on)"] = (_load(pkg, scenes_dir, "20spheres"), ("identity", "pose_a"))
+    # point lights on the surface (see test_edge_cases): shadow directions below the quadratic-branch threshold
+    sc = S.Scene(65, 49, np.radians(0.05), bg, 2)
+    sc.objects = np.array([obj(S.surface_sphere([0, 0, 8], 2.0), 0.2), obj(S.surface_sphere([0.0003, 0, 6.5], 0.4999), 0.0, (0.2, 0.9, 0.3)),
+                           obj(S.surface_sphere([0, 0.5, 6.2], 0.5376), 0.0, (0.2, 0.3, 0.9))] +
+                          [obj(S.surface_sphere([4 + i, 3, 9], 0.5)) for i in range(8)], dtype=S.OBJECT_DTYPE)
+    sc.lights = np.array([S.light_spherical(1e-4, [1e-5, 0, 6.0001], [1, 1, 1]), S.light_spherical(1e-4, [0, 2e-5, 5.9999], [1, 0.5, 1]),
+                          S.light_spherical(30.0, [0, 1.0, 5.5], [1, 1, 0.5])], dtype=S.LIGHT_DTYPE)
+    cases["lights on the surface"] = (sc, ("identity",))
+
+    for label, (sc, poses) in cases.items():
+        port = oracle.PortOracle(sc)
+        with rt.Renderer(sc) as r:
+            info = r.grid_info()
+            assert info["gridded"] + info["loose"] == r.class_counts()["sphere"], info
+            for pose in poses:
+                m = camera.TEST_POSES[pose] if isinstance(pose, str) else pose
+                r.set_option("kernel", 0)
+                r.update(m)
+                exact = r.gather()
+                if isinstance(pose, str):
+                    assert_parity(exact, oracle.quantize_rgba8(port.render(m, threads=os.cpu_count())), label + " exact kernel")
+                r.set_option("kernel", 1)
+                r.set_option("cull_backfacing", 0)
+                r.set_option("accel", 0)
+                r.set_option("grid_density", 0)
+                r.update(m)
+                assert np.array_equal(r.gather(), exact), (label, pose, "brute force")
+                brute = r.counters()
+                for variant, density in ((0, 0), (2, 0), (0, 20), (0, 900)):
+                    r.set_option("accel", 1)
+                    r.set_option("variant", variant)
+                    r.set_option("grid_density", density)
+                    r.update(m)
+                    assert np.array_equal(r.gather(), exact), (label, pose, variant, density, r.grid_info())
+                    c = r.counters()
+                    for k in ("primary_rays", "reflection_rays", "shadow_rays", "hits", "lit"):
+                        assert c[k] == brute[k], (label, pose, k, c, brute)
+                    if label.startswith("synthetic") and density == 0:
+                        assert c["tests_sphere"] < 0.25 * brute["tests_sphere"], (c, brute)
+                r.set_option("variant", 0)
+                r.set_option("cull_backfacing", 1)
+            # the streamed / banded entry point with the grid on
+            import torch
+            host = torch.zeros(sc.px_width * sc.px_height * 4, dtype=torch.uint8).pin_memory()
+            r.update_to_host(m, host.data_ptr(), host.numel())
+            assert np.array_equal(host.numpy().reshape(sc.px_height, sc.px_width, 4), exact), (label, "update_to_host")
