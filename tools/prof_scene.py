@@ -20,6 +20,7 @@ ap.add_argument("--width", type=int, default=3840)
 ap.add_argument("--height", type=int, default=2160)
 ap.add_argument("--bounces", type=int, default=4)
 ap.add_argument("--pose", default="initial")
+ap.add_argument("--accel", type=int, default=-1)
 a = ap.parse_args()
 if a.scene == "synthetic":
     from cuda_ray_tracer_b200 import synth
@@ -29,6 +30,7 @@ else:
         width=a.width, height=a.height, max_reflections=a.bounces)
 with binding.Renderer(sc) as r:
     r.set_option("kernel", a.kernel)
+    r.set_option("accel", a.accel)
     for _ in range(a.frames):
         ms = r.update(camera.TEST_POSES[a.pose])
     print(a.scene, "kernel", a.kernel, "last frame ms", ms, r.counters())
