@@ -127,6 +127,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
 
     Tally tl;
     tl.clear();
+    int last_cubic = -1;   // cubic (class-local index) that gave this thread's previous nearest hit
     const d3 cam_origin = d3{f.origin[0], f.origin[1], f.origin[2]};
     const int n_tiles = cfg.tiles_x * cfg.tiles_y;
     const bool vec_ok = (f.width & 3) == 0;   // rows start 16-byte aligned (packed and assembled layout alike)
@@ -210,7 +211,8 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         // ---- phase A + B: nearest hit, hit record, compact hit list ---------------------------------------
         int obj = -1;
         if (active) {
-            Hit h = nearest_hit_wave<CUBIC, GRID>(g, s, cfg, o, d, primary, !primary || prim_filter, tl);
+            Hit h = nearest_hit_wave<CUBIC, GRID>(g, s, cfg, o, d, primary, !primary || prim_filter, last_cubic, tl);
+            if (CUBIC) last_cubic = h.slot - (g.n_plane + g.n_sphere + g.n_quadric);   // negative: not a cubic
             if (h.slot >= 0) {
                 obj = h.orig;
                 const d3 p = d3{o.x + h.t * d.x, o.y + h.t * d.y, o.z + h.t * d.z};
@@ -244,12 +246,13 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         __syncthreads();
         const int n_hits = ctl.n_hits;
         if (CUBIC && primary && tid == 0 && g.n_cubic > 0) {
-            // the filter costs about a third of an exact test and saves one only for rays that miss
+            // the filter costs about a third of an exact test and saves one only for (ray, cubic) pairs that cannot give
+            // the nearest hit: a ray has one nearest hit, so with several cubics most pairs are of that kind
             int rays = ctl.prim_rays + WAVE, hits = ctl.prim_hits + n_hits;
             if (rays >= 16 * WAVE) { rays >>= 1; hits >>= 1; }
             ctl.prim_rays = rays;
             ctl.prim_hits = hits;
-            ctl.prim_filter = (5 * hits < 3 * rays) ? 1 : 0;     // on while fewer than 60 % of the primary rays hit
+            ctl.prim_filter = (5LL * hits < 3LL * rays * g.n_cubic) ? 1 : 0;   // one cubic: on while fewer than 60 % of the primary rays hit
         }
 
         // ---- phases C + D per chunk of 32 lights ---------------------------------------------------------------

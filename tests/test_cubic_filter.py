@@ -23,12 +23,20 @@ def filt(tmp_path_factory):
     lib = C.CDLL(so)
     lib.rtf_cubic_verdicts.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_double, C.c_int, C.c_void_p]
 
+    lib.rtf_cubic_verdicts_hi.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int, C.c_void_p]
+
     def verdicts(k, o, d, hi, want_hit):
+        """hi: a scalar, or one float32 per ray (the running best t of a nearest-hit search)."""
         k = np.ascontiguousarray(k, dtype=np.float64)
         o = np.ascontiguousarray(o, dtype=np.float64).reshape(-1, 3)
         d = np.ascontiguousarray(d, dtype=np.float64).reshape(-1, 3)
         out = np.zeros(len(o), dtype=np.int32)
-        lib.rtf_cubic_verdicts(k.ctypes.data, o.ctypes.data, d.ctypes.data, len(o), hi, int(want_hit), out.ctypes.data)
+        if np.ndim(hi) == 0:
+            lib.rtf_cubic_verdicts(k.ctypes.data, o.ctypes.data, d.ctypes.data, len(o), hi, int(want_hit), out.ctypes.data)
+        else:
+            hi = np.ascontiguousarray(hi, dtype=np.float32)
+            assert len(hi) == len(o)
+            lib.rtf_cubic_verdicts_hi(k.ctypes.data, o.ctypes.data, d.ctypes.data, len(o), hi.ctypes.data, int(want_hit), out.ctypes.data)
         return out
     return verdicts
 
@@ -119,3 +127,48 @@ def test_filter_on_random_rays_and_transformed_cubics(pkg, oracle, filt):
     bad = np.array([[np.inf, 0, 0], [1e30, 1e30, 1e30], [np.nan, 0, 0], [0, 0, 0]], dtype=np.float64)
     dirs = np.array([[0, 0, 1], [1, 1, 1], [0, 0, 1], [0, 0, 0]], dtype=np.float64)
     assert not filt(k, bad, dirs, MAX_T, True)[:3].any()
+
+
+def float32_round_up(x):
+    """Smallest float32 >= x (what __double2float_ru gives the kernel)."""
+    f = np.asarray(x, dtype=np.float64).astype(np.float32)
+    low = f.astype(np.float64) < x
+    f[low] = np.nextafter(f[low], np.float32(np.inf))
+    return f
+
+
+def test_filter_with_running_nearest_bound(pkg, oracle, filt, scenes_dir):
+    """The nearest-hit search asks the filter about [EPS, best t so far] (rt_wave_device.cuh): a MISS verdict for an
+    interval end hi must mean the exact t is not in [EPS, hi] — hi itself included, because an exact tie in t is
+    resolved by object index and must reach the exact test.  Interval ends: random magnitudes, the exact root rounded
+    up to FP32 (the tie), and values a few ulps either side of a root."""
+    from cuda_ray_tracer_b200 import camera, synth
+    rng = np.random.default_rng(77)
+    surfaces = cubic_objects(synth.synthetic_scene(width=64, height=36))[:9]
+    for name in CUBIC_SCENES:
+        surfaces += cubic_objects(pkg.load_from_file(os.path.join(scenes_dir, name + ".yml")))
+    pruned = total = 0
+    for k in surfaces:
+        o = np.concatenate([np.zeros((300, 3)), rng.uniform(-30, 30, size=(300, 3)) + np.array([0.0, 0.0, 60.0])])
+        d = rng.normal(size=(600, 3)) * np.array([1.0, 0.6, 1.0]) + np.array([0.0, 0.0, 1.5])
+        d /= np.linalg.norm(d, axis=1, keepdims=True)
+        d[450:] *= (10.0 ** rng.uniform(-2, 2, 150))[:, None]
+        t = exact_ts(oracle, k, o, d)
+        has_t = np.isfinite(t) & (t >= EPS) & (t < MAX_T)
+        tt = np.where(has_t, t, 1.0)
+        his = [float32_round_up(np.minimum(MAX_T, 10.0 ** rng.uniform(-6.5, 6, 600))),      # anything
+               float32_round_up(np.minimum(MAX_T, tt)),                                      # the tie: hi = ru(t)
+               np.nextafter(float32_round_up(tt), np.float32(0)),                            # one FP32 ulp below ru(t)
+               float32_round_up(np.minimum(MAX_T, tt * (1.0 - 10.0 ** rng.uniform(-7, -1, 600)))),   # just before the root
+               float32_round_up(np.minimum(MAX_T, tt * (1.0 + 10.0 ** rng.uniform(-7, -1, 600))))]   # just past it
+        for hi in his:
+            hi = np.minimum(hi, np.float32(MAX_T))
+            v = filt(k, o, d, hi, False)
+            inside = (t >= EPS) & (t <= hi.astype(np.float64)) & (t < MAX_T)
+            wrong = (v == 1) & inside
+            assert not wrong.any(), ("MISS but exact t within the bound", t[wrong][:4], hi[wrong][:4])
+            assert not (v == 2).any()                    # want_hit = False never answers HIT
+            pruned += int(((v == 1) & ~inside).sum())
+            total += int((~inside).sum())
+    print("pairs outside the bound proven so:", pruned, "of", total)
+    assert pruned > 0.5 * total

@@ -1,6 +1,6 @@
 """GPU fuzzing of kernel 1 (FP32 cubic filter, light culling, caches) against kernel 0 (exact, thread per pixel):
 random cubic-class surfaces, random lights and cameras, small frames; every frame must be byte-identical.
-    python tools/gpu_fuzz_scenes.py [n_scenes] [seed]"""
+    python tools/gpu_fuzz_scenes.py [n_scenes] [seed] [max_cubics]"""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tools"))
@@ -12,11 +12,12 @@ from cuda_ray_tracer_b200 import scene as S
 
 n_scenes = int(sys.argv[1]) if len(sys.argv) > 1 else 100
 rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 1)
+max_cubics = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 bad = 0
 undecided = tests = 0
 for it in range(n_scenes):
     objs = []
-    for _ in range(rng.integers(1, 4)):
+    for _ in range(rng.integers(1, max_cubics + 1)):
         k = np.zeros(20)
         style = rng.integers(0, 4)
         if style == 0:
