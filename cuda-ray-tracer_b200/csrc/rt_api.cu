@@ -231,6 +231,10 @@ struct rt_b200_ctx {
     cudaEvent_t ev_start = nullptr, ev_render = nullptr, ev_end = nullptr, ev_copy = nullptr;
     cudaEvent_t ev_band[RT_MAX_BANDS] = {};
     int host_bands = 0;                   // 0 = automatic
+    int band_taper = -1;                  // 0 = equal bands; r in 1..99: band k holds (r/100)^k of the rows of band 0;
+                                          // -1 = automatic: whichever of 0 / 65 delivered this scene's recent frames faster
+    float taper_ms[2] = {0.f, 0.f};       // automatic mode: smoothed frame time with [0] equal, [1] tapered bands
+    unsigned taper_frames = 0;
     float ms_render = 0, ms_gather = 0;
 
     ncclComm_t comm = nullptr;
@@ -629,6 +633,43 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
         if (n_bands < 1) n_bands = 1;
     }
     const int band_rows = ((c->local_rows + n_bands - 1) / n_bands + band_unit - 1) / band_unit * band_unit;
+    // Band boundaries.  Equal bands by default; with band_taper the bands shrink geometrically, so that the copy left
+    // over when the last band has rendered — the part of the transfer nothing can hide — is a small one.
+    int band_start[RT_MAX_BANDS + 1];
+    for (int b = 0; b <= n_bands; b++) band_start[b] = std::min(b * band_rows, c->local_rows);
+    // Which is better depends on what bounds the frame: when rendering is slower than the PCIe copy, tapering hides all
+    // but the last small copy; when the copy is slower, equal bands start it earliest.  Automatic mode tries both on the
+    // first two streamed frames, keeps the faster one and re-tries the other every 32nd frame (the camera moves).
+    int taper = c->band_taper;
+    int taper_mode = -1;
+    if (taper < 0) {
+        taper = 0;
+        if (streamed && !blk && n_bands > 1) {
+            const unsigned k = c->taper_frames++;
+            if (k < 2) taper_mode = (int) k;
+            else {
+                taper_mode = c->taper_ms[1] < c->taper_ms[0] ? 1 : 0;
+                if (k % 32 == 0) taper_mode ^= 1;
+            }
+            taper = taper_mode ? 65 : 0;
+        }
+    }
+    if (streamed && !blk && taper > 0 && n_bands > 1) {
+        const int units = (c->local_rows + band_unit - 1) / band_unit;
+        const double r = taper / 100.0;
+        double w[RT_MAX_BANDS], sum = 0.0;
+        for (int b = 0; b < n_bands; b++) sum += (w[b] = std::pow(r, b));
+        double acc = 0.0;
+        int prev = 0;
+        for (int b = 1; b < n_bands; b++) {
+            acc += w[b - 1];
+            int u = (int) std::llround(acc / sum * units);
+            u = std::max(prev + 1, std::min(u, units - (n_bands - b)));
+            band_start[b] = std::min(u * band_unit, c->local_rows);
+            prev = u;
+        }
+        band_start[n_bands] = c->local_rows;
+    }
     unsigned host_seq = 0;
     if (blk) {
         host_seq = ++blk->seq;
@@ -655,8 +696,8 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
         CUDA_TRY(rt::build_queue_tables(c->view, c->qtables, *c->qscene, 1, 2, f.origin, c->stream));
     c->launches = 0;
     for (int b = 0; b < n_bands; b++) {
-        f.row0 = b * band_rows;
-        f.rows = std::min(band_rows, c->local_rows - f.row0);
+        f.row0 = band_start[b];
+        f.rows = band_start[b + 1] - band_start[b];
         if (f.rows <= 0) break;
         rc = launch_kernel(c, f);
         if (rc != RT_B200_OK) return rc;
@@ -754,6 +795,7 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
     CUDA_TRY(cudaEventElapsedTime(&c->ms_gather, c->ev_render, c->ev_end));
     float total = c->ms_render + c->ms_gather;
     if (streamed) CUDA_TRY(cudaEventElapsedTime(&total, c->ev_start, c->ev_copy));
+    if (taper_mode >= 0) c->taper_ms[taper_mode] = c->taper_ms[taper_mode] > 0.f ? 0.5f * (c->taper_ms[taper_mode] + total) : total;
     const double t_synced = tracing ? now_seconds() : 0.0;
     if (blk) {
         // this rank's strips are in host memory (the event wait above); publish that, and rank 0 — whose caller
@@ -1073,6 +1115,12 @@ int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
     else if (!std::strcmp(name, "host_bands")) {
         if (value < 0 || value > RT_MAX_BANDS) return fail(RT_B200_ERR_ARG, "host_bands must be 0..%d", RT_MAX_BANDS);
         c->host_bands = (int) value;
+    }
+    else if (!std::strcmp(name, "band_taper")) {
+        if (value < -1 || value > 99) return fail(RT_B200_ERR_ARG, "band_taper must be -1..99");
+        c->band_taper = (int) value;
+        c->taper_frames = 0;
+        c->taper_ms[0] = c->taper_ms[1] = 0.f;
     }
     else if (!std::strcmp(name, "count")) {
         c->count = value != 0;

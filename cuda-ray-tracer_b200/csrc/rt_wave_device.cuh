@@ -89,11 +89,8 @@ static __device__ __noinline__ GridOccluderResult occluder_spheres_grid(const Sc
 // CUBIC = false compiles the cubic class out (scenes without cubics run a leaner kernel).
 // GRID = true compiles the grid walk in (its own kernel instantiations, so the brute-force kernels carry none of it).
 template <bool CUBIC, bool GRID>
-// prefer: the cubic to test first (the one that gave this thread's previous nearest hit; neighbouring rays mostly see the
-// same surface, and once the best t is small the filter prunes the other cubics), -1 = index order.  The order of the
-// tests cannot change the result: the tie rule looks at the original index.
 __device__ __forceinline__ Hit nearest_hit_wave(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg,
-                                                const d3 &o, const d3 &d, bool primary, bool filter, int prefer, Tally &tl)
+                                                const d3 &o, const d3 &d, bool primary, bool filter, Tally &tl)
 {
     Hit h;
     h.t = CUDART_INF;
@@ -146,20 +143,22 @@ __device__ __forceinline__ Hit nearest_hit_wave(const SceneView &g, const SceneS
         const float ofx = (float) o.x, ofy = (float) o.y, ofz = (float) o.z;
         const float dfx = (float) d.x, dfy = (float) d.y, dfz = (float) d.z;
         unsigned exact = 0;
-        const int first = (prefer > 0 && prefer < g.n_cubic) ? prefer : 0;
-        const int cubic_base = slot;
-        for (int k = 0; k < g.n_cubic; k++) {
-            const int i = k == 0 ? first : (k <= first ? k - 1 : k);
-            slot = cubic_base + i;
+        for (int i = 0; i < g.n_cubic; i++, slot++) {
             if (cfg.use_cubic_filter && filter) {
-                // A candidate matters only if its t is below the best t so far (or ties with it): the filter is asked about
-                // [EPS, best_t] — rounded up to FP32, and the proven-empty interval extends 2e-6 (relative) past its end — so
-                // in scenes with many cubic surfaces only the few that can still improve the hit reach the exact test.
-                const float hi = fminf((float) RT_MAX_T, __double2float_ru(h.t));
                 const float *kf = s.cubic_f + RT_CF_FLOATS * i;
                 const CubicD cd = make_cubic_d(kf, dfx, dfy, dfz);
-                const int v = primary ? cubic_verdict_od(s.cam_o[i], cd, hi, false)
-                                      : cubic_verdict_od(make_cubic_o(kf, ofx, ofy, ofz), cd, hi, false);
+                const CubicO co = primary ? s.cam_o[i] : make_cubic_o(kf, ofx, ofy, ofz);
+                int v;
+                if (g.n_cubic > 1) {
+                    // Several cubic surfaces: a candidate matters only if its t is below the best t so far (or ties with
+                    // it), so the filter is asked about [EPS, best_t] — rounded up to FP32, and the proven-empty interval
+                    // extends 2e-6 (relative) past its end — and only the few surfaces that can still improve the hit
+                    // reach the exact test.
+                    v = cubic_verdict_od(co, cd, fminf((float) RT_MAX_T, __double2float_ru(h.t)), false);
+                }
+                else {
+                    v = cubic_verdict_od(co, cd, (float) RT_MAX_T, false);   // constant end: the compiler folds it
+                }
                 if (v == CV_MISS) continue;
             }
             exact++;

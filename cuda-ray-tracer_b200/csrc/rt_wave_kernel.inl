@@ -127,7 +127,6 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
 
     Tally tl;
     tl.clear();
-    int last_cubic = -1;   // cubic (class-local index) that gave this thread's previous nearest hit
     const d3 cam_origin = d3{f.origin[0], f.origin[1], f.origin[2]};
     const int n_tiles = cfg.tiles_x * cfg.tiles_y;
     const bool vec_ok = (f.width & 3) == 0;   // rows start 16-byte aligned (packed and assembled layout alike)
@@ -211,8 +210,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         // ---- phase A + B: nearest hit, hit record, compact hit list ---------------------------------------
         int obj = -1;
         if (active) {
-            Hit h = nearest_hit_wave<CUBIC, GRID>(g, s, cfg, o, d, primary, !primary || prim_filter, last_cubic, tl);
-            if (CUBIC) last_cubic = h.slot - (g.n_plane + g.n_sphere + g.n_quadric);   // negative: not a cubic
+            Hit h = nearest_hit_wave<CUBIC, GRID>(g, s, cfg, o, d, primary, !primary || prim_filter, tl);
             if (h.slot >= 0) {
                 obj = h.orig;
                 const d3 p = d3{o.x + h.t * d.x, o.y + h.t * d.y, o.z + h.t * d.z};

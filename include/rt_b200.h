@@ -155,6 +155,10 @@ int rt_b200_get_counters(rt_b200_ctx *ctx, rt_b200_counters *out);
  *                       update-cpu.cpp:48-56,66-72; 0 = brute force (what the roofline figures are quoted on);
  *                       -1 (default) = on for scenes with at least 64 sphere-class objects.  With the grid on, the
  *                       tests_sphere / confirms counters report the candidates actually examined
+ *           "band_taper"  rt_b200_update_to_host: 0 = equal row bands; r in 1..99 = band k holds (r/100)^k of the rows
+ *                       of band 0, so the device-to-host copy that remains after the last band has rendered is small
+ *                       (pays when rendering is slower than the copy); -1 (default) = try 0 and 65 on the first two
+ *                       frames, keep the faster, re-try the other every 32nd frame
  *           "grid_density"  rebuild the grid at value / 100 cells per sphere (0 = default 1.5)                      */
 int rt_b200_set_option(rt_b200_ctx *ctx, const char *name, int64_t value);
 

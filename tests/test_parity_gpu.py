@@ -201,12 +201,13 @@ def test_update_to_host_streams_the_same_frame(pkg, rt, scenes_dir, kernel):
             r.update(camera.TEST_POSES["pose_a"])
             ref = r.gather()
             c_ref = r.counters()
-            for bands in (0, 1, 3, 16):
+            for bands, taper in ((0, 0), (1, 0), (3, 0), (16, 0), (8, 70), (5, 40), (16, 99), (0, 65), (0, -1), (0, -1), (0, -1)):
                 r.set_option("host_bands", bands)
+                r.set_option("band_taper", taper)      # geometrically shrinking bands: same pixels, other boundaries
                 host.zero_()
                 ms = r.update_to_host(camera.TEST_POSES["pose_a"], host.data_ptr(), host.numel())
                 assert ms > 0.0
-                assert np.array_equal(host.numpy().reshape(h, w, 4), ref), (name, bands)
+                assert np.array_equal(host.numpy().reshape(h, w, 4), ref), (name, bands, taper)
                 c = r.counters()      # the ray census is band-independent (test counts depend on the shadow cache)
                 assert all(c[k] == c_ref[k] for k in ("primary_rays", "reflection_rays", "shadow_rays", "hits", "lit"))
             with pytest.raises(rt.RtError):

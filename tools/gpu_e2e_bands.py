@@ -1,4 +1,4 @@
-"""End-to-end frame time (rt_b200_update_to_host into pinned memory) against the number of row bands."""
+"""End-to-end frame time (rt_b200_update_to_host into pinned memory) against the number of row bands and their taper."""
 import json, os, sys, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tools"))
@@ -16,12 +16,13 @@ for name in names:
     with binding.Renderer(sc) as r:
         r.set_option("count", 0)
         row["device_ms"] = round(min(r.update(m) for _ in range(5)), 4)
-        for bands in (1, 2, 3, 4, 6, 8, 12, 16):
+        for bands, taper in ((1, 0), (4, 0), (6, 0), (8, 0), (12, 0), (6, 70), (8, 70), (8, 60), (8, 80), (10, 70), (0, -1)):
             r.set_option("host_bands", bands)
+            r.set_option("band_taper", taper)
             for _ in range(2):
                 r.update_to_host(m, host.data_ptr(), host.numel())
             t0 = time.perf_counter()
             for _ in range(10):
                 r.update_to_host(m, host.data_ptr(), host.numel())
-            row["b%d" % bands] = round((time.perf_counter() - t0) * 100, 4)
+            row["b%d_t%d" % (bands, taper)] = round((time.perf_counter() - t0) * 100, 4)
     print(json.dumps(row), flush=True)

@@ -33,8 +33,11 @@ base = int(body[0][ia], 16)
 counters = {int(r[ia], 16) - base: (int(r[iex] or 0), int(r[ismp] or 0), r[isrc].strip()) for r in body}
 
 # mangled-name fragment to find the section: template args of render_wave_kernel<W, MINB, COUNT>
-m = re.search(r"render_wave_kernel<\(int\)(\d+), \(int\)(\d+), \(bool\)(\d)>", kernel)
-frag = "render_wave_kernelILi{}ELi{}ELb{}E".format(*m.groups()) if m else re.sub(r"\W.*", "", kernel.split("::")[-1])
+m = re.search(r"(\w+)<([^>]*)>", kernel)
+if m:   # mangled template arguments: (int)N -> LiNE, (bool)B -> LbBE
+    frag = m.group(1) + "I" + "".join(("Li%sE" if t == "int" else "Lb%sE") % v for t, v in re.findall(r"\((int|bool)\)(\d+)", m.group(2))) + "E"
+else:
+    frag = re.sub(r"\W.*", "", kernel.split("(")[0].split("::")[-1])
 
 tmp = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(a.so)], cwd=tmp, capture_output=True)
