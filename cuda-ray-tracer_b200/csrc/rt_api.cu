@@ -227,13 +227,16 @@ struct rt_b200_ctx {
     int flag_barrier = 1;            // 1: flag words (default), 0: 4-byte NCCL all-reduce
     const uchar4 *last_frame = nullptr;   // what rt_b200_gather hands out
 
-    cudaStream_t stream = nullptr, copy_stream = nullptr;
+    cudaStream_t stream = nullptr, copy_stream = nullptr, stream2 = nullptr;   // stream2: odd bands of a streamed frame
+    cudaEvent_t ev_join = nullptr;
+    int band_overlap = 1;                 // streamed frames: alternate the bands between two streams (tail overlap)
     cudaEvent_t ev_start = nullptr, ev_render = nullptr, ev_end = nullptr, ev_copy = nullptr;
     cudaEvent_t ev_band[RT_MAX_BANDS] = {};
     int host_bands = 0;                   // 0 = automatic
-    int band_taper = -1;                  // 0 = equal bands; r in 1..99: band k holds (r/100)^k of the rows of band 0;
-                                          // -1 = automatic: whichever of 0 / 65 delivered this scene's recent frames faster
-    float taper_ms[2] = {0.f, 0.f};       // automatic mode: smoothed frame time with [0] equal, [1] tapered bands
+    int band_taper = -1;                  // 0 = equal bands; r in 1..99: band k holds (r/100)^k of the rows of band 0
+                                          // (shrinking); 100 + r: the same sizes in reverse order (growing);
+                                          // -1 = automatic: whichever of 0 / 65 / 165 delivered this scene's recent frames fastest
+    float taper_ms[3] = {0.f, 0.f, 0.f};  // automatic mode: smoothed frame time with [0] equal, [1] shrinking, [2] growing bands
     unsigned taper_frames = 0;
     float ms_render = 0, ms_gather = 0;
 
@@ -438,8 +441,9 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     up(upload(orig_index, &c->d_orig), "index map");
     up(upload(ldev, &c->d_lights), "lights");
     up(upload(cubic_mask, &c->d_cubic_mask), "cubic masks");
-    up(cudaMalloc((void **) &c->d_tile_counter, 2 * sizeof(unsigned long long)), "tile counter");
-    if (c->d_tile_counter) up(cudaMemset(c->d_tile_counter, 0, 2 * sizeof(unsigned long long)), "tile counter");
+    // one {next tile, CTAs finished} pair per band, so that the bands of a streamed frame may overlap; pair 0 otherwise
+    up(cudaMalloc((void **) &c->d_tile_counter, 2 * RT_MAX_BANDS * sizeof(unsigned long long)), "tile counter");
+    if (c->d_tile_counter) up(cudaMemset(c->d_tile_counter, 0, 2 * RT_MAX_BANDS * sizeof(unsigned long long)), "tile counter");
     c->sphere_r2_max = r2_max;
     // queue kernel tables: [2 + n_lights] rows of n_sphere_pad entries
     c->qtables.n_sphere_pad = ((int) sphere.size() + 3) & ~3;
@@ -472,6 +476,8 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     up(cudaEventCreate(&c->ev_end), "event");
     up(cudaEventCreate(&c->ev_copy), "event");
     up(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking), "copy stream");
+    up(cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking), "second render stream");
+    up(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming), "event");
     for (int b = 0; b < RT_MAX_BANDS; b++) up(cudaEventCreateWithFlags(&c->ev_band[b], cudaEventDisableTiming), "event");
     up(cudaMalloc((void **) &c->d_barrier, sizeof(int)), "barrier word");
     up(cudaHostAlloc((void **) &c->h_timed_out, sizeof(unsigned), cudaHostAllocMapped), "timeout word");
@@ -529,10 +535,12 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
 namespace {
 
 // One render launch of the selected kernel over the packed rows [f.row0, f.row0 + f.rows).
-int launch_kernel(rt_b200_ctx *c, const rt::FrameParams &f)
+// stream / counter_pair: the stream to launch on and which tile-counter pair the wavefront kernel uses (bands that may
+// run concurrently need their own).
+int launch_kernel(rt_b200_ctx *c, const rt::FrameParams &f, cudaStream_t stream, int counter_pair)
 {
     if (c->kernel_kind == 0) {
-        CUDA_TRY(rt::launch_render_exact(c->view, f, c->stream));
+        CUDA_TRY(rt::launch_render_exact(c->view, f, stream));
     }
     else if (c->kernel_kind == 2 && c->qscene) {
         rt::QueueLaunch ql{};
@@ -543,14 +551,14 @@ int launch_kernel(rt_b200_ctx *c, const rt::FrameParams &f)
         ql.shadow_cache = c->shadow_cache;
         ql.variant = c->queue_variant;
         c->tile_counter_dirty = true;
-        CUDA_TRY(rt::launch_render_queue(c->view, f, ql, c->stream));
+        CUDA_TRY(rt::launch_render_queue(c->view, f, ql, stream));
     }
     else {   // kernel 1, and kernel 2 for scenes that exceed the queue kernel's parameter block
         if (c->tile_counter_dirty) {
-            CUDA_TRY(cudaMemsetAsync(c->d_tile_counter, 0, 2 * sizeof(unsigned long long), c->stream));
+            CUDA_TRY(cudaMemsetAsync(c->d_tile_counter, 0, 2 * RT_MAX_BANDS * sizeof(unsigned long long), stream));
             c->tile_counter_dirty = false;
         }
-        rt::WaveLaunch wl{c->d_tile_counter, c->d_cubic_mask, c->sphere_r2_max, c->shadow_cache, c->wave_variant, c->cubic_filter,
+        rt::WaveLaunch wl{c->d_tile_counter + 2 * counter_pair, c->d_cubic_mask, c->sphere_r2_max, c->shadow_cache, c->wave_variant, c->cubic_filter,
                           (c->cull_backfacing && c->cull_safe) ? 1 : 0,
                           (c->accel > 0 || (c->accel < 0 && c->view.n_sphere >= RT_GRID_AUTO_SPHERES)) ? 1 : 0,
                           nullptr, nullptr, nullptr, 0u};
@@ -560,7 +568,7 @@ int launch_kernel(rt_b200_ctx *c, const rt::FrameParams &f)
             wl.sync_timed_out = c->d_timed_out;
             wl.sync_seq = c->seq;
         }
-        const cudaError_t e = rt::launch_render_wave(c->view, f, wl, c->stream);
+        const cudaError_t e = rt::launch_render_wave(c->view, f, wl, stream);
         if (e != cudaSuccess) {
             c->tile_counter_dirty = true;
             return fail(RT_B200_ERR_CUDA, "launch_render_wave: %s", cudaGetErrorString(e));
@@ -637,28 +645,32 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
     // over when the last band has rendered — the part of the transfer nothing can hide — is a small one.
     int band_start[RT_MAX_BANDS + 1];
     for (int b = 0; b <= n_bands; b++) band_start[b] = std::min(b * band_rows, c->local_rows);
-    // Which is better depends on what bounds the frame: when rendering is slower than the PCIe copy, tapering hides all
-    // but the last small copy; when the copy is slower, equal bands start it earliest.  Automatic mode tries both on the
-    // first two streamed frames, keeps the faster one and re-tries the other every 32nd frame (the camera moves).
+    // Which is better depends on what bounds the frame.  Rendering slower than the PCIe copy: shrinking bands hide all but
+    // the last, small copy.  Copy slower than rendering: the frame takes (first band's render) + (whole copy), so growing
+    // bands — a tiny first one — start the copy engine earliest.  Automatic mode tries the three shapes on the first
+    // streamed frames of a scene, keeps the fastest and re-tries another every 32nd frame (the camera moves).
     int taper = c->band_taper;
     int taper_mode = -1;
     if (taper < 0) {
         taper = 0;
         if (streamed && !blk && n_bands > 1) {
             const unsigned k = c->taper_frames++;
-            if (k < 2) taper_mode = (int) k;
+            if (k < 3) taper_mode = (int) k;
             else {
-                taper_mode = c->taper_ms[1] < c->taper_ms[0] ? 1 : 0;
-                if (k % 32 == 0) taper_mode ^= 1;
+                taper_mode = 0;
+                for (int mde = 1; mde < 3; mde++)
+                    if (c->taper_ms[mde] < c->taper_ms[taper_mode]) taper_mode = mde;
+                if (k % 32 == 0) taper_mode = (taper_mode + 1 + (int) ((k / 32) & 1)) % 3;
             }
-            taper = taper_mode ? 65 : 0;
+            taper = taper_mode == 0 ? 0 : (taper_mode == 1 ? 65 : 165);
         }
     }
     if (streamed && !blk && taper > 0 && n_bands > 1) {
         const int units = (c->local_rows + band_unit - 1) / band_unit;
-        const double r = taper / 100.0;
+        const bool growing = taper > 100;
+        const double r = (growing ? taper - 100 : taper) / 100.0;
         double w[RT_MAX_BANDS], sum = 0.0;
-        for (int b = 0; b < n_bands; b++) sum += (w[b] = std::pow(r, b));
+        for (int b = 0; b < n_bands; b++) sum += (w[b] = std::pow(r, growing ? n_bands - 1 - b : b));
         double acc = 0.0;
         int prev = 0;
         for (int b = 1; b < n_bands; b++) {
@@ -695,15 +707,21 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
     if (c->kernel_kind == 2 && c->qscene)   // the primary-ray table depends on the camera origin: one setup launch per frame
         CUDA_TRY(rt::build_queue_tables(c->view, c->qtables, *c->qscene, 1, 2, f.origin, c->stream));
     c->launches = 0;
+    const bool overlap = streamed && !blk && n_bands > 1 && c->band_overlap && c->kernel_kind == 1 && !c->tile_counter_dirty;
     for (int b = 0; b < n_bands; b++) {
         f.row0 = band_start[b];
         f.rows = band_start[b + 1] - band_start[b];
         if (f.rows <= 0) break;
-        rc = launch_kernel(c, f);
+        // Overlap: even bands on the render stream, odd bands on a second one, each band with its own tile counter.  The
+        // persistent CTAs of band b fill the GPU, so band b + 1 only gets the SM slots band b's tail leaves empty —
+        // the bands still finish in order, but the tail of one no longer idles the machine before the next starts.
+        cudaStream_t bs = (overlap && (b & 1)) ? c->stream2 : c->stream;
+        if (overlap && b == 1) CUDA_TRY(cudaStreamWaitEvent(c->stream2, c->ev_start, 0));
+        rc = launch_kernel(c, f, bs, overlap ? b : 0);
         if (rc != RT_B200_OK) return rc;
         c->launches++;
         if (streamed) {
-            CUDA_TRY(cudaEventRecord(c->ev_band[b], c->stream));
+            CUDA_TRY(cudaEventRecord(c->ev_band[b], bs));
             CUDA_TRY(cudaStreamWaitEvent(c->copy_stream, c->ev_band[b], 0));
             const size_t off = (size_t) f.row0 * c->width;
             if (!blk) {
@@ -746,6 +764,10 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
                 }
             }
         }
+    }
+    if (overlap) {
+        CUDA_TRY(cudaEventRecord(c->ev_join, c->stream2));
+        CUDA_TRY(cudaStreamWaitEvent(c->stream, c->ev_join, 0));
     }
     CUDA_TRY(cudaEventRecord(c->ev_render, c->stream));
     c->last_frame = c->d_local;
@@ -1024,6 +1046,8 @@ int rt_b200_destroy(rt_b200_ctx *c)
     for (int b = 0; b < RT_MAX_BANDS; b++)
         if (c->ev_band[b]) cudaEventDestroy(c->ev_band[b]);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    if (c->stream2) cudaStreamDestroy(c->stream2);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
     cudaFree(c->d_barrier);
     if (c->h_timed_out) cudaFreeHost(c->h_timed_out);
     if (c->d_shared_base) {
@@ -1116,11 +1140,14 @@ int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
         if (value < 0 || value > RT_MAX_BANDS) return fail(RT_B200_ERR_ARG, "host_bands must be 0..%d", RT_MAX_BANDS);
         c->host_bands = (int) value;
     }
+    else if (!std::strcmp(name, "band_overlap")) {
+        c->band_overlap = value ? 1 : 0;
+    }
     else if (!std::strcmp(name, "band_taper")) {
-        if (value < -1 || value > 99) return fail(RT_B200_ERR_ARG, "band_taper must be -1..99");
+        if (value < -1 || value > 199 || value == 100) return fail(RT_B200_ERR_ARG, "band_taper must be -1..99 or 101..199");
         c->band_taper = (int) value;
         c->taper_frames = 0;
-        c->taper_ms[0] = c->taper_ms[1] = 0.f;
+        c->taper_ms[0] = c->taper_ms[1] = c->taper_ms[2] = 0.f;
     }
     else if (!std::strcmp(name, "count")) {
         c->count = value != 0;

@@ -157,8 +157,11 @@ int rt_b200_get_counters(rt_b200_ctx *ctx, rt_b200_counters *out);
  *                       tests_sphere / confirms counters report the candidates actually examined
  *           "band_taper"  rt_b200_update_to_host: 0 = equal row bands; r in 1..99 = band k holds (r/100)^k of the rows
  *                       of band 0, so the device-to-host copy that remains after the last band has rendered is small
- *                       (pays when rendering is slower than the copy); -1 (default) = try 0 and 65 on the first two
- *                       frames, keep the faster, re-try the other every 32nd frame
+ *                       (pays when rendering is slower than the copy); 100 + r = the same sizes in reverse order, a tiny
+ *                       band first (pays when the copy is slower: it starts earliest); -1 (default) = try 0, 65 and 165
+ *                       on a scene's first streamed frames, keep the fastest, re-try another every 32nd frame
+ *           "band_overlap"  rt_b200_update_to_host, wavefront kernel: 1 (default) = consecutive row bands alternate between
+ *                       two streams, each with its own tile counter, so the tail of one band overlaps the start of the next
  *           "grid_density"  rebuild the grid at value / 100 cells per sphere (0 = default 1.5)                      */
 int rt_b200_set_option(rt_b200_ctx *ctx, const char *name, int64_t value);
 

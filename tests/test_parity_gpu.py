@@ -201,9 +201,10 @@ def test_update_to_host_streams_the_same_frame(pkg, rt, scenes_dir, kernel):
             r.update(camera.TEST_POSES["pose_a"])
             ref = r.gather()
             c_ref = r.counters()
-            for bands, taper in ((0, 0), (1, 0), (3, 0), (16, 0), (8, 70), (5, 40), (16, 99), (0, 65), (0, -1), (0, -1), (0, -1)):
+            for bands, taper in ((0, 0), (1, 0), (3, 0), (16, 0), (8, 70), (5, 40), (16, 99), (0, 65), (7, 150), (16, 199), (0, -1), (0, -1), (0, -1), (0, -1)):
                 r.set_option("host_bands", bands)
                 r.set_option("band_taper", taper)      # geometrically shrinking bands: same pixels, other boundaries
+                r.set_option("band_overlap", bands % 2)  # bands alternating between two streams, or all on one
                 host.zero_()
                 ms = r.update_to_host(camera.TEST_POSES["pose_a"], host.data_ptr(), host.numel())
                 assert ms > 0.0

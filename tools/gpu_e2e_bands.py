@@ -16,13 +16,15 @@ for name in names:
     with binding.Renderer(sc) as r:
         r.set_option("count", 0)
         row["device_ms"] = round(min(r.update(m) for _ in range(5)), 4)
-        for bands, taper in ((1, 0), (4, 0), (6, 0), (8, 0), (12, 0), (6, 70), (8, 70), (8, 60), (8, 80), (10, 70), (0, -1)):
-            r.set_option("host_bands", bands)
-            r.set_option("band_taper", taper)
-            for _ in range(2):
-                r.update_to_host(m, host.data_ptr(), host.numel())
-            t0 = time.perf_counter()
-            for _ in range(10):
-                r.update_to_host(m, host.data_ptr(), host.numel())
-            row["b%d_t%d" % (bands, taper)] = round((time.perf_counter() - t0) * 100, 4)
+        for overlap in (1,):
+            r.set_option("band_overlap", overlap)
+            for bands, taper in ((8, 0), (12, 0), (8, 65), (8, 165), (8, 150), (8, 180), (12, 165), (12, 175), (0, -1)):
+                r.set_option("host_bands", bands)
+                r.set_option("band_taper", taper)
+                for _ in range(3):
+                    r.update_to_host(m, host.data_ptr(), host.numel())
+                t0 = time.perf_counter()
+                for _ in range(10):
+                    r.update_to_host(m, host.data_ptr(), host.numel())
+                row["o%d_b%d_t%d" % (overlap, bands, taper)] = round((time.perf_counter() - t0) * 100, 4)
     print(json.dumps(row), flush=True)
