@@ -311,7 +311,7 @@ def run_b200(args):
     clocks = sampler.stop() if rank == 0 else None
 
     # ---- end-to-end timing (host buffers) ----------------------------------------------------------
-    for _ in range(2):
+    for _ in range(max(args.warmup, 3)):      # also lets update_to_host settle its band shape per scene (three frames)
         step_e2e()
     barrier()
     t0 = time.perf_counter()
