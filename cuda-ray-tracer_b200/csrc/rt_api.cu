@@ -707,7 +707,7 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
     if (c->kernel_kind == 2 && c->qscene)   // the primary-ray table depends on the camera origin: one setup launch per frame
         CUDA_TRY(rt::build_queue_tables(c->view, c->qtables, *c->qscene, 1, 2, f.origin, c->stream));
     c->launches = 0;
-    const bool overlap = streamed && !blk && n_bands > 1 && c->band_overlap && c->kernel_kind == 1 && !c->tile_counter_dirty;
+    const bool overlap = streamed && n_bands > 1 && c->band_overlap && c->kernel_kind == 1 && !c->tile_counter_dirty;
     for (int b = 0; b < n_bands; b++) {
         f.row0 = band_start[b];
         f.rows = band_start[b + 1] - band_start[b];

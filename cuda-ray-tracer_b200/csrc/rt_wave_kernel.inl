@@ -480,9 +480,11 @@ cudaError_t launch_render_wave_t(const SceneView &scene, const FrameParams &fram
         return cudaErrorInvalidConfiguration;
     const size_t cta256 = wave_fixed_smem<256>() + scene_smem + wave_cubic_smem(scene, 256) + 1024;   // + per-CTA reservation
     // the grid walk is compiled into the 256-thread variants only (nothing is staged for the spheres, so three CTAs fit)
+    // (two CTAs per SM at 128 registers by default: the walk spills at the 80 registers of the three-CTA variant —
+    // C5 at 4K 15.3 vs 16.1 ms)
     if (cfg.use_grid) {
-        if (wl.variant == 2) return launch_wave_variant<256, 2, CUBIC, true>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
-        return launch_wave_variant<256, 3, CUBIC, true>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
+        if (wl.variant == 3) return launch_wave_variant<256, 3, CUBIC, true>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
+        return launch_wave_variant<256, 2, CUBIC, true>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
     }
     int variant = wl.variant;
     if (variant <= 0) variant = (3 * cta256 <= (size_t) sm_smem) ? 3 : 5;

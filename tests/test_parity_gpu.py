@@ -422,7 +422,7 @@ def test_sphere_grid_frames_identical(pkg, rt, oracle, scenes_dir):
                 r.update(m)
                 assert np.array_equal(r.gather(), exact), (label, pose, "brute force")
                 brute = r.counters()
-                for variant, density in ((0, 0), (2, 0), (0, 20), (0, 900)):
+                for variant, density in ((0, 0), (3, 0), (0, 20), (0, 900)):
                     r.set_option("accel", 1)
                     r.set_option("variant", variant)
                     r.set_option("grid_density", density)

@@ -25,7 +25,7 @@ for name, sc in todo:
         print(json.dumps({"scene": name, "accel": 0, "ms": round(ms, 4), "rays": c["rays"], "tests_sphere": c["tests_sphere"],
                           "confirms": c["fp64_confirms"], "tests_cubic": c["tests_cubic"], "cubic_exact": c["cubic_exact"]}), flush=True)
         r.set_option("accel", 1)
-        for variant, density in ((0, 0), (2, 0), (0, 50), (0, 400), (0, 1000), (2, 400)):
+        for variant, density in ((0, 0), (3, 0), (0, 50), (0, 400), (0, 1000), (3, 400)):
             r.set_option("variant", variant)
             r.set_option("grid_density", density)
             r.set_option("count", 1)

@@ -3,6 +3,6 @@
 cd "${GRAFT_REPO_ROOT:-/root/repo}"
 O=gpurun_out
 mkdir -p $O
-timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/multi_gpu_check.py > $O/s24_check.log 2>&1; echo "check exit $?" | tee -a $O/s24_status.txt
-timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus 2 --steps 20 --warmup 3 > $O/s24_bench2.json 2> $O/s24_bench2.err; echo "bench2 exit $?" | tee -a $O/s24_status.txt
-grep -c "identical=True" $O/s24_check.log; grep -c "identical=False" $O/s24_check.log; tail -3 $O/s24_check.log
+timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/multi_gpu_check.py > $O/s27_check.log 2>&1; echo "check exit $?" | tee -a $O/s27_status.txt
+timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus 2 --steps 20 --warmup 3 > $O/s27_bench2.json 2> $O/s27_bench2.err; echo "bench2 exit $?" | tee -a $O/s27_status.txt
+grep -c "identical=True" $O/s27_check.log; grep -c "identical=False" $O/s27_check.log; tail -3 $O/s27_check.log
