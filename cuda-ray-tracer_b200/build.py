@@ -15,9 +15,9 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "librt_b200.so")
-SOURCES = ["rt_api.cu", "rt_kernels.cu", "rt_wave.cu", "rt_wave_plain.cu", "rt_queue.cu"]
+SOURCES = ["rt_api.cu", "rt_kernels.cu", "rt_wave.cu", "rt_wave_plain.cu", "rt_wave_grid.cu", "rt_wave_grid_plain.cu", "rt_queue.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false", "-std=c++17",
-              "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall", "--threads", "5", "--use_fast_math=false"]
+              "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall", "--threads", "7", "--use_fast_math=false"]
 
 
 def _stale() -> bool:

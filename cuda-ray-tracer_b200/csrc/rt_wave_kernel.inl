@@ -447,6 +447,27 @@ cudaError_t launch_wave_variant(const SceneView &scene, const FrameParams &frame
 // Variant choice: 256-thread CTAs, three per SM, while the staged scene leaves room for that; otherwise one
 // 512-thread CTA per SM so that a large scene is staged once and still 16 warps are resident.  (256 x {1, 4} were
 // measured in round 1 and never won; they are no longer compiled.)
+} // namespace
+
+// The kernels with the grid walk are instantiated in their own translation units (rt_wave_grid.cu with the cubic class,
+// rt_wave_grid_plain.cu without), so that the four units compile in parallel.
+cudaError_t launch_wave_grid_cubic(const SceneView &scene, const FrameParams &frame, const WaveConfig &cfg, size_t scene_smem,
+                                   int n_sm, int max_smem, int variant, cudaStream_t stream);
+cudaError_t launch_wave_grid_plain(const SceneView &scene, const FrameParams &frame, const WaveConfig &cfg, size_t scene_smem,
+                                   int n_sm, int max_smem, int variant, cudaStream_t stream);
+#ifdef RT_WAVE_GRID_TU
+// two CTAs per SM at 128 registers by default: the walk spills at the 80 registers of the three-CTA variant (C5 at 4K
+// 15.2 vs 16.1 ms)
+cudaError_t RT_WAVE_GRID_TU(const SceneView &scene, const FrameParams &frame, const WaveConfig &cfg, size_t scene_smem,
+                            int n_sm, int max_smem, int variant, cudaStream_t stream)
+{
+    if (variant == 3) return launch_wave_variant<256, 3, RT_WAVE_GRID_CUBIC, true>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
+    return launch_wave_variant<256, 2, RT_WAVE_GRID_CUBIC, true>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
+}
+#endif
+
+namespace {
+
 template <bool CUBIC>
 cudaError_t launch_render_wave_t(const SceneView &scene, const FrameParams &frame, const WaveLaunch &wl, cudaStream_t stream)
 {
@@ -480,12 +501,9 @@ cudaError_t launch_render_wave_t(const SceneView &scene, const FrameParams &fram
         return cudaErrorInvalidConfiguration;
     const size_t cta256 = wave_fixed_smem<256>() + scene_smem + wave_cubic_smem(scene, 256) + 1024;   // + per-CTA reservation
     // the grid walk is compiled into the 256-thread variants only (nothing is staged for the spheres, so three CTAs fit)
-    // (two CTAs per SM at 128 registers by default: the walk spills at the 80 registers of the three-CTA variant —
-    // C5 at 4K 15.3 vs 16.1 ms)
-    if (cfg.use_grid) {
-        if (wl.variant == 3) return launch_wave_variant<256, 3, CUBIC, true>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
-        return launch_wave_variant<256, 2, CUBIC, true>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
-    }
+    if (cfg.use_grid)
+        return CUBIC ? launch_wave_grid_cubic(scene, frame, cfg, scene_smem, n_sm, max_smem, wl.variant, stream)
+                     : launch_wave_grid_plain(scene, frame, cfg, scene_smem, n_sm, max_smem, wl.variant, stream);
     int variant = wl.variant;
     if (variant <= 0) variant = (3 * cta256 <= (size_t) sm_smem) ? 3 : 5;
     switch (variant) {
