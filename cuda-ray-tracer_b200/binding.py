@@ -29,7 +29,7 @@ EXPORTS = ("rt_b200_upload_scene", "rt_b200_update", "rt_b200_gather", "rt_b200_
            "rt_b200_get_timing", "rt_b200_get_class_counts", "rt_b200_strip_layout", "rt_b200_version",
            "rt_b200_update_to_host", "rt_b200_frame_export", "rt_b200_frame_attach", "rt_b200_get_launches",
            "rt_b200_host_alloc", "rt_b200_host_free", "rt_b200_host_alloc_shared", "rt_b200_host_free_shared",
-           "rt_b200_get_grid_info")
+           "rt_b200_get_grid_info", "rt_b200_band_layout")
 
 UNIQUE_ID_BYTES = 128
 IPC_HANDLE_BYTES = 64
@@ -68,6 +68,7 @@ def load_library():
     L.rt_b200_get_timing.argtypes = [vp, C.POINTER(C.c_float * 2)]
     L.rt_b200_get_class_counts.argtypes = [vp, C.POINTER(C.c_uint32 * 4)]
     L.rt_b200_get_grid_info.argtypes = [vp, C.POINTER(C.c_uint32 * 6)]
+    L.rt_b200_band_layout.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.POINTER(C.c_int32)]
     L.rt_b200_version.restype = C.c_char_p
     L.rt_b200_update_to_host.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(C.c_float)]
     L.rt_b200_frame_export.argtypes = [vp, vp]
@@ -99,6 +100,13 @@ def strip_layout(height: int, strip_rows: int, rank: int, world_size: int) -> np
     rows = np.empty(n.value, dtype=np.int32)
     _check(L.rt_b200_strip_layout(height, strip_rows, rank, world_size, _dp(rows), rows.size, C.byref(n)))
     return rows
+
+
+def band_layout(rows: int, n_bands: int, unit: int = 16, taper: int = 0) -> np.ndarray:
+    """Row-band boundaries of a streamed frame (n_bands + 1 row indices).  Host-only; needs no GPU."""
+    starts = np.empty(n_bands + 1, dtype=np.int32)
+    _check(load_library().rt_b200_band_layout(rows, n_bands, unit, taper, starts.ctypes.data_as(C.POINTER(C.c_int32))))
+    return starts
 
 
 def comm_unique_id() -> bytes:

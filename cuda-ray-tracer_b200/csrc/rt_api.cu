@@ -308,6 +308,31 @@ int build_grid(rt_b200_ctx *c, double density)
     return RT_B200_OK;
 }
 
+// Row-band boundaries of a streamed frame (rt_b200_update_to_host): n_bands bands over `rows` rows, every boundary a
+// multiple of `unit` rows.  taper 0: equal bands; 1..99: band k holds (taper/100)^k of the rows of band 0 (shrinking);
+// 101..199: the same sizes in reverse order (growing).  Every band gets at least one unit (n_bands <= ceil(rows / unit)).
+void band_layout(int rows, int n_bands, int unit, int taper, int *start /* [n_bands + 1] */)
+{
+    const int band_rows = ((rows + n_bands - 1) / n_bands + unit - 1) / unit * unit;
+    for (int b = 0; b <= n_bands; b++) start[b] = std::min(b * band_rows, rows);
+    if (taper <= 0 || n_bands < 2) return;
+    const int units = (rows + unit - 1) / unit;
+    const bool growing = taper > 100;
+    const double r = (growing ? taper - 100 : taper) / 100.0;
+    double w[RT_MAX_BANDS], sum = 0.0;
+    for (int b = 0; b < n_bands; b++) sum += (w[b] = std::pow(r, growing ? n_bands - 1 - b : b));
+    double acc = 0.0;
+    int prev = 0;
+    for (int b = 1; b < n_bands; b++) {
+        acc += w[b - 1];
+        int u = (int) std::llround(acc / sum * units);
+        u = std::max(prev + 1, std::min(u, units - (n_bands - b)));
+        start[b] = std::min(u * unit, rows);
+        prev = u;
+    }
+    start[n_bands] = rows;
+}
+
 rt::ObjClass classify(const double *k)
 {
     for (int i = rt::X3; i <= rt::XYZ; i++)
@@ -640,11 +665,8 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
         if (n_bands > (c->local_rows + band_unit - 1) / band_unit) n_bands = (c->local_rows + band_unit - 1) / band_unit;
         if (n_bands < 1) n_bands = 1;
     }
-    const int band_rows = ((c->local_rows + n_bands - 1) / n_bands + band_unit - 1) / band_unit * band_unit;
-    // Band boundaries.  Equal bands by default; with band_taper the bands shrink geometrically, so that the copy left
-    // over when the last band has rendered — the part of the transfer nothing can hide — is a small one.
+    // Band boundaries (band_layout).  Equal bands unless a taper is chosen below.
     int band_start[RT_MAX_BANDS + 1];
-    for (int b = 0; b <= n_bands; b++) band_start[b] = std::min(b * band_rows, c->local_rows);
     // Which is better depends on what bounds the frame.  Rendering slower than the PCIe copy: shrinking bands hide all but
     // the last, small copy.  Copy slower than rendering: the frame takes (first band's render) + (whole copy), so growing
     // bands — a tiny first one — start the copy engine earliest.  Automatic mode tries the three shapes on the first
@@ -665,23 +687,7 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
             taper = taper_mode == 0 ? 0 : (taper_mode == 1 ? 65 : 165);
         }
     }
-    if (streamed && !blk && taper > 0 && n_bands > 1) {
-        const int units = (c->local_rows + band_unit - 1) / band_unit;
-        const bool growing = taper > 100;
-        const double r = (growing ? taper - 100 : taper) / 100.0;
-        double w[RT_MAX_BANDS], sum = 0.0;
-        for (int b = 0; b < n_bands; b++) sum += (w[b] = std::pow(r, growing ? n_bands - 1 - b : b));
-        double acc = 0.0;
-        int prev = 0;
-        for (int b = 1; b < n_bands; b++) {
-            acc += w[b - 1];
-            int u = (int) std::llround(acc / sum * units);
-            u = std::max(prev + 1, std::min(u, units - (n_bands - b)));
-            band_start[b] = std::min(u * band_unit, c->local_rows);
-            prev = u;
-        }
-        band_start[n_bands] = c->local_rows;
-    }
+    band_layout(c->local_rows, n_bands, band_unit, (streamed && !blk) ? taper : 0, band_start);
     unsigned host_seq = 0;
     if (blk) {
         host_seq = ++blk->seq;
@@ -1206,6 +1212,17 @@ int rt_b200_get_grid_info(rt_b200_ctx *c, uint32_t out[6])
 {
     if (!c || !out) return fail(RT_B200_ERR_ARG, "null argument");
     std::memcpy(out, c->grid_info, sizeof(c->grid_info));
+    return RT_B200_OK;
+}
+
+int rt_b200_band_layout(uint32_t rows, uint32_t n_bands, uint32_t unit, int taper, int32_t *starts)
+{
+    if (!starts || rows == 0 || unit == 0 || n_bands == 0 || n_bands > RT_MAX_BANDS || taper < 0 || taper > 199 || taper == 100)
+        return fail(RT_B200_ERR_ARG, "bad band layout query");
+    if (n_bands > (rows + unit - 1) / unit) return fail(RT_B200_ERR_ARG, "%u bands do not fit %u rows in units of %u", n_bands, rows, unit);
+    int tmp[RT_MAX_BANDS + 1];
+    band_layout((int) rows, (int) n_bands, (int) unit, taper, tmp);
+    for (uint32_t b = 0; b <= n_bands; b++) starts[b] = tmp[b];
     return RT_B200_OK;
 }
 

@@ -4,6 +4,7 @@
 //               [--frames K] [--position x,y,z] [--yaw deg] [--pitch deg]       (camera: ray-tracer.cpp:25-32)
 //               [--orbit]                                                       (scripted fly-through: yaw sweeps 60..120)
 //               [--out frame.ppm] [--raw frame.rgba] [--kernel 0|1|2]
+//               [--option name=value ...]                                       (any rt_b200_set_option, e.g. accel=1)
 //               [--dump-scene]                                                  (print the parsed scene; needs no GPU)
 //
 // What stays of the reference's main: argv[1] is the scene path and a SceneException ends the program with its
@@ -17,6 +18,8 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <utility>
+#include <vector>
 
 #include "rt_camera.h"
 #include "rt_host_scene.h"
@@ -29,7 +32,7 @@ void usage(const char *argv0)
     std::fprintf(stderr,
                  "Usage: %s <scene.yml> [--width W] [--height H] [--max-reflections N] [--frames K]\n"
                  "          [--position x,y,z] [--yaw deg] [--pitch deg] [--orbit] [--out f.ppm] [--raw f.rgba]\n"
-                 "          [--kernel 0|1|2] [--dump-scene]\n", argv0);
+                 "          [--kernel 0|1|2] [--option name=value ...] [--dump-scene]\n", argv0);
 }
 
 void dump_scene(const rt_host::Scene &s)
@@ -85,6 +88,7 @@ int main(int argc, char **argv)
     long width = 0, height = 0, max_refl = -1, frames = 1, kernel = -1;
     bool orbit = false, dump = false;
     const char *out_ppm = nullptr, *out_raw = nullptr;
+    std::vector<std::pair<std::string, long long>> options;
     rt_host::Camera cam;
     for (int i = 2; i < argc; i++) {
         const std::string a = argv[i];
@@ -112,6 +116,15 @@ int main(int argc, char **argv)
         else if (a == "--out") out_ppm = next();
         else if (a == "--raw") out_raw = next();
         else if (a == "--dump-scene") dump = true;
+        else if (a == "--option") {
+            const std::string kv = next();
+            const size_t eq = kv.find('=');
+            if (eq == std::string::npos || eq == 0) {
+                usage(argv[0]);
+                return EXIT_FAILURE;
+            }
+            options.emplace_back(kv.substr(0, eq), std::atoll(kv.c_str() + eq + 1));
+        }
         else {
             usage(argv[0]);
             return EXIT_FAILURE;
@@ -132,6 +145,7 @@ int main(int argc, char **argv)
             return EXIT_FAILURE;
         }
         if (kernel >= 0) update_set_option("kernel", kernel);
+        for (const auto &o : options) update_set_option(o.first.c_str(), o.second);
         init_update(0, scene);   // ray-tracer.cpp:215
 
         double m[16];

@@ -174,6 +174,11 @@ int rt_b200_get_launches(rt_b200_ctx *ctx, uint32_t *launches);
 /* Structural class counts of the uploaded scene: planes, spheres, quadrics, cubics. */
 int rt_b200_get_class_counts(rt_b200_ctx *ctx, uint32_t out[4]);
 
+/* Host-only helper (needs no GPU): the row bands rt_b200_update_to_host cuts a frame of `rows` rows into — n_bands
+ * (1..16) bands, boundaries at multiples of `unit` rows, shape as option "band_taper" (0 equal, 1..99 shrinking,
+ * 101..199 growing).  starts receives n_bands + 1 row indices, starts[0] = 0, starts[n_bands] = rows. */
+int rt_b200_band_layout(uint32_t rows, uint32_t n_bands, uint32_t unit, int taper, int32_t *starts);
+
 /* The sphere grid built at upload (option "accel"): cells along x, y, z; spheres registered in cells; spheres kept on
  * the always-tested list (too large, too small or non-finite for the grid); cell registrations in total. */
 int rt_b200_get_grid_info(rt_b200_ctx *ctx, uint32_t out[6]);

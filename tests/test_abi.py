@@ -113,3 +113,33 @@ def test_shared_host_block_arguments(pkg, lib, tmp_path):
         with pytest.raises(binding.RtError, match="rt_b200 error 2"):
             binding.host_alloc_shared(str(path), 10000, True)
         assert not path.exists()
+
+
+def test_band_layout(pkg, lib):
+    """Row bands of the streamed host delivery (rt_b200_update_to_host): cover the rows exactly once, boundaries on whole
+    units, every band non-empty; equal / shrinking / growing shapes as option band_taper describes them."""
+    from cuda_ray_tracer_b200 import binding
+    for rows, unit in ((2160, 16), (4320, 16), (1080, 16), (563, 16), (16, 16), (37, 8), (270, 40)):
+        units = -(-rows // unit)
+        for n in (1, 2, 3, 5, 8, 12, 16):
+            if n > units:
+                with pytest.raises(binding.RtError):
+                    binding.band_layout(rows, n, unit, 0)
+                continue
+            for taper in (0, 1, 40, 65, 99, 101, 150, 165, 199):
+                s = binding.band_layout(rows, n, unit, taper)
+                assert s[0] == 0 and s[-1] == rows and len(s) == n + 1
+                if taper == 0:       # equal bands rounded up to whole units may cover the rows in fewer than n bands
+                    assert (np.diff(s) >= 0).all() and (s[s < rows] % unit == 0).all()
+                    continue
+                assert (np.diff(s) > 0).all(), (rows, unit, n, taper, s)
+                assert (s[:-1] % unit == 0).all()
+    eq = np.diff(binding.band_layout(2160, 8, 16, 0))
+    assert eq.max() - eq.min() <= 2160 - 7 * 272 and eq[0] == 272
+    sh = np.diff(binding.band_layout(2160, 8, 16, 65))
+    gr = np.diff(binding.band_layout(2160, 8, 16, 165))
+    assert (np.diff(sh) <= 0).all() and sh[0] > 4 * sh[-1] and sh[-1] <= 64          # a small last band
+    assert (np.diff(gr[:-1]) >= 0).all() and gr[0] <= 64 and gr[-2] > 4 * gr[0]       # a small first band
+    for bad in ((0, 1, 16, 0), (100, 0, 16, 0), (100, 17, 1, 0), (100, 2, 0, 0), (100, 2, 16, 100), (100, 2, 16, 200), (100, 2, 16, -1)):
+        with pytest.raises(binding.RtError):
+            binding.band_layout(*bad)

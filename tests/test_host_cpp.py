@@ -172,7 +172,8 @@ def test_headless_driver_frame_equals_python_host(pkg, exe, scenes_dir, tmp_path
         ppm = tmp_path / (name + ".ppm")
         out = subprocess.run([exe, os.path.join(scenes_dir, name + ".yml"), "--width", "640", "--height", "360",
                               "--max-reflections", "4", "--frames", "3", "--position", "{},{},{}".format(*pos),
-                              "--yaw", str(yaw), "--pitch", str(pitch), "--raw", str(raw), "--out", str(ppm)],
+                              "--yaw", str(yaw), "--pitch", str(pitch), "--raw", str(raw), "--out", str(ppm),
+                              "--option", "accel=1", "--option", "band_taper=65"],   # speed options: no pixel changes
                              capture_output=True, text=True)
         assert out.returncode == 0, out.stderr
         assert out.stdout.startswith("FPS: ") and "last render time:" in out.stdout
@@ -188,3 +189,10 @@ def test_headless_driver_frame_equals_python_host(pkg, exe, scenes_dir, tmp_path
         assert data.startswith(b"P6\n640 360\n255\n")
         px = np.frombuffer(data[len(b"P6\n640 360\n255\n"):], dtype=np.uint8).reshape(360, 640, 3)
         assert np.array_equal(px, got[::-1, :, :3])
+
+
+def test_headless_driver_rejects_malformed_option(exe, scenes_dir):
+    """--option wants name=value; anything else prints the usage text (needs no GPU)."""
+    for bad in ("accel", "=1"):
+        out = subprocess.run([exe, os.path.join(scenes_dir, "dingdong.yml"), "--option", bad], capture_output=True, text=True)
+        assert out.returncode != 0 and "--option name=value" in out.stderr
