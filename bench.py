@@ -164,8 +164,9 @@ def run_reference(args):
     scenes, desc = build_workload(pkg, args.workload)
     cores = os.cpu_count() or 1
     kind = "reference" if oracle_py.have_ref() else "port"
-    ystep = args.ref_row_step or 2
     m = camera.TEST_POSES["initial"]
+    # each step a bounded sample: about 1.5 s of wall time on all host threads (every 2nd row for the bundled step)
+    ystep = args.ref_row_step or max(2, pick_row_step(oracle_py, scenes, m, cores, 1.5))
     # ray census of the sampled rows (untimed, via the counting restatement)
     rays_sample = 0
     for _, sc in scenes:
@@ -187,8 +188,9 @@ def run_reference(args):
         step()
     dt = sum(step() for _ in range(args.steps)) / args.steps
     value = rays_sample / dt / 1e6
-    sample = "every {}th image row of each frame ({} rows per 2160), {} host threads".format(
-        ystep, len(range(0, HEIGHT, ystep)), cores)
+    h0 = scenes[0][1].px_height
+    sample = "every {}th image row of each frame ({} rows per {}), {} host threads".format(
+        ystep, len(range(0, h0, ystep)), h0, cores)
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
@@ -268,6 +270,13 @@ def run_b200(args):
                 r.update(host_cam.numpy())
                 if rank == 0:           # the frame is assembled on GPU 0 (north_star); rank 0 hands it to the host
                     r.gather_into(host_frame.data_ptr(), nbytes)
+
+    # ---- frame check (untimed): every frame this run times is first compared with the exact per-pixel kernel, with
+    # the reference CPU build on a pixel sample, and — at N > 1 — rank 0's ASSEMBLED frame with a 1-GPU render of the
+    # same frame (fused gather, and once through the NCCL all-gather path).  A mismatch ends the run with exit code 3.
+    frame_check = None
+    if not args.no_frame_check:
+        frame_check = check_frames(args, pkg, binding, renderers, m, rank, local, world, barrier, dist if world > 1 else None)
 
     # ---- census (untimed): rays and tests of one step, with the kernel's counters on -----------------
     # The metric counts the rays the REFERENCE casts for these frames: census with culling off.  The
@@ -380,6 +389,8 @@ def run_b200(args):
                        "parallelism": "strips{}x{}rows,{}".format(world, args.strip_rows, "p2p-store+flags" if fused else
                                                                   "nccl-allgather") if world > 1 else "1gpu",
                        "timing": "CUDA events on the render stream per frame, summed; max over ranks",
+                       "ms_per_step_wall": ms_wall, "frame_check": frame_check,
+                       "value_traced": rays_traced / ms_step / 1e3,
                        "l2": "outputs ({} MB per step) exceed the 126 MB L2; the scene (KBs) is cache-resident by design"
                              .format(len(renderers) * frame_bytes // 1000000)},
             "e2e": {"value": rays_step / ms_e2e / 1e3, "unit": UNIT, "ms_per_step": ms_e2e,
@@ -417,27 +428,126 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+def check_frames(args, pkg, binding, renderers, m, rank, local, world, barrier, dist) -> dict:
+    """Untimed.  oracle/ is used here as the checker only (never timed, never shipped)."""
+    import numpy as np
+    out = {"scenes": len(renderers), "vs_exact_kernel": "identical", "vs_ref_pixels": 0, "outliers": 0, "max_diff": 0,
+           "assembled_equals_1gpu": None if world == 1 else True, "nccl_allgather_equals_1gpu": None,
+           "oracle": None, "mismatches": []}
+    oracle_py = None
+    if rank == 0:
+        from oracle import oracle_py
+        oracle_py.build()
+        out["oracle"] = "reference build (oracle/_ref)" if oracle_py.have_ref() else "restatement (oracle/rt_oracle.c)"
+    n_px = 1000 if args.workload == "bundled4k" else 1200
+    for i, (label, sc, r) in enumerate(renderers):
+        r.set_option("kernel", args.kernel)
+        r.set_option("accel", args.accel)
+        r.set_option("cull_backfacing", 1 if args.cull else 0)
+        r.update(m)
+        img = None
+        if rank == 0:
+            img = r.gather()            # world > 1: the frame assembled on rank 0 (rank 0's update returns when it is whole)
+        barrier()
+        nccl_img = None
+        if world > 1 and i == 0:        # the all-gather assembly path, once: a second context without the fused frame
+            r2 = binding.Renderer(sc, device=local, rank=rank, world_size=world)
+            r2.set_option("strip_rows", args.strip_rows)
+            ident = [binding.comm_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(ident, src=0)
+            r2.comm_init(ident[0])
+            r2.update(m)
+            if rank == 0:
+                nccl_img = r2.gather()
+            barrier()
+            r2.close()
+        if rank == 0:
+            with binding.Renderer(sc, device=local) as r1:
+                r1.set_option("kernel", 0)
+                r1.update(m)
+                exact = r1.gather()
+                if world > 1:
+                    r1.set_option("kernel", args.kernel)
+                    r1.set_option("accel", args.accel)
+                    r1.update(m)
+                    single = r1.gather()
+                    if not np.array_equal(img, single):
+                        out["assembled_equals_1gpu"] = False
+                        out["mismatches"].append(label + ": assembled frame differs from the 1-GPU frame")
+                    if nccl_img is not None:
+                        out["nccl_allgather_equals_1gpu"] = bool(np.array_equal(nccl_img, single))
+                        if not out["nccl_allgather_equals_1gpu"]:
+                            out["mismatches"].append(label + ": NCCL all-gather frame differs from the 1-GPU frame")
+            if not np.array_equal(img, exact):
+                out["vs_exact_kernel"] = "differs"
+                out["mismatches"].append("{}: {} pixels differ from kernel 0".format(label, int((img != exact).any(axis=-1).sum())))
+            rng = np.random.default_rng(1000 + i)
+            xy = np.stack([rng.integers(0, sc.px_width, n_px), rng.integers(0, sc.px_height, n_px)], axis=1).astype(np.int32)
+            o = oracle_py.RefCpu(sc) if oracle_py.have_ref() else oracle_py.PortOracle(sc)
+            want = oracle_py.quantize_rgba8(o.render_pixels(m, xy))
+            d = np.abs(img[xy[:, 1], xy[:, 0]].astype(np.int16) - want.astype(np.int16)).max(axis=-1)
+            out["vs_ref_pixels"] += int(n_px)
+            out["outliers"] += int((d > 1).sum())
+            out["max_diff"] = max(out["max_diff"], int(d.max()))
+            if (d > 1).sum() > max(1, n_px // 1000):
+                out["mismatches"].append("{}: {} of {} sampled pixels beyond +-1 LSB of the CPU reference".format(label, int((d > 1).sum()), n_px))
+    bad = [len(out["mismatches"])]
+    if world > 1:
+        dist.broadcast_object_list(bad, src=0)
+    if bad[0]:
+        if rank == 0:
+            print(json.dumps({"frame_check": out}), file=sys.stderr, flush=True)
+        raise SystemExit(3)
+    del out["mismatches"]
+    return out
+
+
+def pick_row_step(oracle_py, scenes, m, threads: int, budget_s: float) -> int:
+    """Row stride that bounds one CPU pass over the workload to about `budget_s` seconds on `threads` host threads:
+    a 96-pixel probe per scene estimates the cost of a whole frame (C5 at 7680x4320 would take hours)."""
+    import numpy as np
+    est = 0.0
+    for _, sc in scenes:
+        rng = np.random.default_rng(5)
+        xy = np.stack([rng.integers(0, sc.px_width, 96), rng.integers(0, sc.px_height, 96)], axis=1).astype(np.int32)
+        t0 = time.perf_counter()
+        oracle_py.PortOracle(sc).render_pixels(m, xy)
+        est += (time.perf_counter() - t0) / 96 * sc.px_width * sc.px_height
+    return max(1, int(np.ceil(est / threads / budget_s)))
+
+
 def cpu_baseline(pkg, scenes, args) -> dict:
-    """The reference CPU path on this box's host cores, bounded row sample (about 10-30 s of CPU work)."""
+    """The reference CPU path on this box's host cores, bounded row sample (about 10-30 s of CPU work): all host
+    threads (rows split over threads; the reference itself is a serial loop, update-cpu.cpp:125-133) and, beside it,
+    one thread "as shipped" on a sparser sample."""
     from cuda_ray_tracer_b200 import camera
     from oracle import oracle_py
     oracle_py.build()
     cores = os.cpu_count() or 1
     kind = "reference" if oracle_py.have_ref() else "port"
     m = camera.TEST_POSES["initial"]
-    ystep = args.ref_row_step or 1
-    rays, secs = 0, 0.0
-    for _, sc in scenes:
-        _, _, cnt = oracle_py.PortOracle(sc).render_rows(m, 0, sc.px_height, ystep, threads=cores, count=True)
-        rays += cnt["primary_rays"] + cnt["reflection_rays"] + cnt["shadow_rays"]
-        if kind == "reference":
-            _, ms = oracle_py.RefCpu(sc).render_rows(m, 0, sc.px_height, ystep, threads=cores)
-        else:
-            _, ms = oracle_py.PortOracle(sc).render_rows(m, 0, sc.px_height, ystep, threads=cores)
-        secs += ms / 1e3
-    return {"value": rays / secs / 1e6, "unit": UNIT, "cores": cores, "kind": kind,
-            "sample": "{} of each frame of the workload, {} host threads, {:.1f} s".format(
-                "every image row" if ystep == 1 else "every {}th image row".format(ystep), cores, secs)}
+
+    def leg(ystep, threads):
+        rays, secs = 0, 0.0
+        for _, sc in scenes:
+            _, _, cnt = oracle_py.PortOracle(sc).render_rows(m, 0, sc.px_height, ystep, threads=cores, count=True)
+            rays += cnt["primary_rays"] + cnt["reflection_rays"] + cnt["shadow_rays"]
+            if kind == "reference":
+                _, ms = oracle_py.RefCpu(sc).render_rows(m, 0, sc.px_height, ystep, threads=threads)
+            else:
+                _, ms = oracle_py.PortOracle(sc).render_rows(m, 0, sc.px_height, ystep, threads=threads)
+            secs += ms / 1e3
+        what = "every image row" if ystep == 1 else "every {}th image row".format(ystep)
+        return rays / secs / 1e6, "{} of each frame of the workload, {} host thread{}, {:.1f} s".format(
+            what, threads, "" if threads == 1 else "s", secs)
+
+    ystep = args.ref_row_step or pick_row_step(oracle_py, scenes, m, cores, 10.0)
+    value, sample = leg(ystep, cores)
+    ystep1 = pick_row_step(oracle_py, scenes, m, 1, 6.0)
+    value1, sample1 = leg(ystep1, 1)
+    return {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
+            "one_thread": {"value": value1, "unit": UNIT, "cores": 1, "sample": sample1,
+                           "what": "the reference as shipped: a serial loop over the pixels (update-cpu.cpp:125-133)"}}
 
 
 def main():
@@ -458,6 +568,7 @@ def main():
                     "0 = brute force like the reference (default, what the roofline is quoted on), 1 = on, -1 = library default")
     ap.add_argument("--no-cull", dest="cull", action="store_false", help="trace every shadow ray the reference casts")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-frame-check", action="store_true", help="skip the untimed frame verification before the timed loops")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

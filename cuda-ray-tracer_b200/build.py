@@ -15,9 +15,9 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "librt_b200.so")
-SOURCES = ["rt_api.cu", "rt_kernels.cu", "rt_wave.cu", "rt_wave_plain.cu", "rt_wave_grid.cu", "rt_wave_grid_plain.cu", "rt_queue.cu"]
+SOURCES = ["rt_api.cu", "rt_kernels.cu", "rt_wave.cu", "rt_wave_plain.cu", "rt_wave_grid.cu", "rt_wave_grid_plain.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false", "-std=c++17",
-              "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall", "--threads", "7", "--use_fast_math=false"]
+              "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall", "--threads", "7"]
 
 
 def _stale() -> bool:
@@ -32,8 +32,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not _stale():
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    flags = [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")]
-    cmd = [nvcc] + flags + (["-Xptxas", "-v"] if verbose else []) + ["-shared", "-o", LIB] + \
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-shared", "-o", LIB] + \
           [os.path.join(CSRC, s) for s in SOURCES] + ["-ldl"]
     subprocess.run(cmd, check=True)
     return LIB

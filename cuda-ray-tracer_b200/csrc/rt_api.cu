@@ -31,7 +31,6 @@
 #include "../../include/rt_b200.h"
 #include "rt_grid_build.h"
 #include "rt_kernels.h"
-#include "rt_queue.cuh"
 
 namespace {
 
@@ -172,7 +171,7 @@ struct rt_b200_ctx {
     // device scene
     rt::SceneView view{};
     double4 *d_plane = nullptr, *d_sphere = nullptr;
-    float4 *d_sphere_f = nullptr, *d_material = nullptr;
+    float4 *d_sphere_f = nullptr, *d_material = nullptr, *d_material_pi = nullptr;
     double *d_quadric = nullptr, *d_cubic = nullptr, *d_coef_full = nullptr;
     int *d_orig = nullptr;
     rt::LightDev *d_lights = nullptr;
@@ -186,9 +185,6 @@ struct rt_b200_ctx {
     unsigned long long *d_counters = nullptr;
     unsigned long long *d_tile_counter = nullptr;
     unsigned *d_cubic_mask = nullptr;
-    rt::QueueTables qtables{};       // queue kernel: FP32 sphere tables (rt_tables.cuh)
-    rt::QueueScene *qscene = nullptr;   // queue kernel: scene block passed in the kernel parameters (null: does not fit)
-    int queue_variant = 0;
     float sphere_r2_max = 0.0f;
     int shadow_cache = -1;
     int wave_variant = 0;
@@ -384,7 +380,7 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
 
     // ---- classify and repack --------------------------------------------------------------------
     std::vector<double4> plane, sphere;
-    std::vector<float4> sphere_f, material(n_objects);
+    std::vector<float4> sphere_f, material(n_objects), material_pi(n_objects);
     std::vector<double> quadric, cubic, coef_full(20 * n_objects);
     std::vector<int> orig[4];
     std::vector<unsigned> cubic_mask;
@@ -399,6 +395,8 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
         std::memcpy(color, obj_bytes + RT_B200_OBJECT_BYTES * i + 164, 12);
         std::memcpy(&coef_full[20 * i], k, 160);
         material[i] = make_float4(refl, color[0], color[1], color[2]);
+        const float pi_f = 3.14159274101257324f;   // glm::pi<float>(); IEEE FP32 division here as on the device
+        material_pi[i] = make_float4(refl, color[0] / pi_f, color[1] / pi_f, color[2] / pi_f);
         if (!(fabsf(color[0]) < 1e5f && fabsf(color[1]) < 1e5f && fabsf(color[2]) < 1e5f)) c->cull_safe = false;
         rt::ObjClass cls = classify(k);
         orig[cls].push_back((int) i);
@@ -463,6 +461,7 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     up(upload(cubic, &c->d_cubic), "cubics");
     up(upload(coef_full, &c->d_coef_full), "coefficients");
     up(upload(material, &c->d_material), "materials");
+    up(upload(material_pi, &c->d_material_pi), "materials / pi");
     up(upload(orig_index, &c->d_orig), "index map");
     up(upload(ldev, &c->d_lights), "lights");
     up(upload(cubic_mask, &c->d_cubic_mask), "cubic masks");
@@ -470,30 +469,6 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     up(cudaMalloc((void **) &c->d_tile_counter, 2 * RT_MAX_BANDS * sizeof(unsigned long long)), "tile counter");
     if (c->d_tile_counter) up(cudaMemset(c->d_tile_counter, 0, 2 * RT_MAX_BANDS * sizeof(unsigned long long)), "tile counter");
     c->sphere_r2_max = r2_max;
-    // queue kernel tables: [2 + n_lights] rows of n_sphere_pad entries
-    c->qtables.n_sphere_pad = ((int) sphere.size() + 3) & ~3;
-    c->qtables.r2_max = r2_max;
-    c->qtables.r_max = nextafterf(sqrtf(r2_max), INFINITY);
-    c->qtables.center_norm_max = center_norm_max;
-    c->qtables.tables_safe = tables_safe ? 1 : 0;
-    up(cudaMalloc((void **) &c->qtables.tables,
-                  sizeof(float4) * (size_t) (2 + n_lights) * (c->qtables.n_sphere_pad ? c->qtables.n_sphere_pad : 4)),
-       "sphere tables");
-    // queue kernel scene block (kernel parameters): everything except the spheres
-    if (plane.size() <= rt::QK_MAX_PLANE && quadric.size() <= 10 * (size_t) rt::QK_MAX_QUADRIC &&
-        cubic_mask.size() <= rt::QK_MAX_CUBIC && n_lights <= (size_t) rt::QK_MAX_LIGHT) {
-        rt::QueueScene *qs = new rt::QueueScene();
-        std::memset(qs, 0, sizeof(*qs));
-        for (size_t i = 0; i < plane.size(); i++) qs->plane[i] = plane[i];
-        for (size_t i = 0; i < quadric.size(); i++) qs->quadric[i / 10][i % 10] = quadric[i];
-        for (size_t i = 0; i < cubic.size(); i++) qs->cubic[i / 20][i % 20] = cubic[i];
-        for (size_t i = 0; i < cubic_mask.size(); i++) qs->cubic_mask[i] = cubic_mask[i];
-        for (size_t j = 0; j < n_lights; j++) {
-            qs->light[j] = ldev[j];
-            qs->lf[j] = rt::make_light_filter(ldev[j]);
-        }
-        c->qscene = qs;
-    }
     up(cudaMalloc((void **) &c->d_counters, sizeof(unsigned long long) * rt::CNT_COUNT), "counters");
     up(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "stream");
     up(cudaEventCreate(&c->ev_start), "event");
@@ -531,22 +506,12 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     v.orig_index = c->d_orig;
     v.coef_full = c->d_coef_full;
     v.material = c->d_material;
+    v.material_pi = c->d_material_pi;
     v.lights = c->d_lights;
     v.sphere_center_max = center_max;
 
     rc = build_grid(c, 0.0);
     if (rc == RT_B200_OK) rc = ensure_buffers(c);
-    if (rc == RT_B200_OK) {
-        // light families and every table row that does not depend on the camera (rows 0 and 2..)
-        const double zero[3] = {0.0, 0.0, 0.0};
-        cudaError_t e = cudaSuccess;
-        if (c->qscene) {
-            e = rt::build_queue_tables(v, c->qtables, *c->qscene, 0, 1, zero, c->stream);
-            if (e == cudaSuccess) e = rt::build_queue_tables(v, c->qtables, *c->qscene, 2, 2 + v.n_lights, zero, c->stream);
-        }
-        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
-        if (e != cudaSuccess) rc = fail(RT_B200_ERR_CUDA, "sphere tables: %s", cudaGetErrorString(e));
-    }
     if (rc != RT_B200_OK) {
         rt_b200_destroy(c);
         return rc;
@@ -567,18 +532,7 @@ int launch_kernel(rt_b200_ctx *c, const rt::FrameParams &f, cudaStream_t stream,
     if (c->kernel_kind == 0) {
         CUDA_TRY(rt::launch_render_exact(c->view, f, stream));
     }
-    else if (c->kernel_kind == 2 && c->qscene) {
-        rt::QueueLaunch ql{};
-        ql.tile_counter = c->d_tile_counter;
-        ql.tables = c->qtables;
-        ql.scene = c->qscene;
-        ql.primary_safe = (fabs(f.origin[0]) < 1e9 && fabs(f.origin[1]) < 1e9 && fabs(f.origin[2]) < 1e9) ? 1 : 0;
-        ql.shadow_cache = c->shadow_cache;
-        ql.variant = c->queue_variant;
-        c->tile_counter_dirty = true;
-        CUDA_TRY(rt::launch_render_queue(c->view, f, ql, stream));
-    }
-    else {   // kernel 1, and kernel 2 for scenes that exceed the queue kernel's parameter block
+    else {
         if (c->tile_counter_dirty) {
             CUDA_TRY(cudaMemsetAsync(c->d_tile_counter, 0, 2 * RT_MAX_BANDS * sizeof(unsigned long long), stream));
             c->tile_counter_dirty = false;
@@ -702,7 +656,7 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
     if (c->count) CUDA_TRY(cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long) * rt::CNT_COUNT, c->stream));
     CUDA_TRY(cudaEventRecord(c->ev_start, c->stream));
     // kernel 1 does the go / flag hand-shake of the fused gather in its own prologue / epilogue: no extra launches
-    c->sync_in_kernel = shared && c->flag_barrier && (c->kernel_kind == 1 || (c->kernel_kind == 2 && !c->qscene));
+    c->sync_in_kernel = shared && c->flag_barrier && c->kernel_kind == 1;
     if (shared && c->flag_barrier) {
         c->seq++;
         if (!c->sync_in_kernel) {
@@ -710,8 +664,6 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
             else CUDA_TRY(rt::launch_sync_wait(c->d_go, 0, 1, c->seq - 1, c->d_timed_out, c->stream));
         }
     }
-    if (c->kernel_kind == 2 && c->qscene)   // the primary-ray table depends on the camera origin: one setup launch per frame
-        CUDA_TRY(rt::build_queue_tables(c->view, c->qtables, *c->qscene, 1, 2, f.origin, c->stream));
     c->launches = 0;
     const bool overlap = streamed && n_bands > 1 && c->band_overlap && c->kernel_kind == 1 && !c->tile_counter_dirty;
     for (int b = 0; b < n_bands; b++) {
@@ -1036,6 +988,7 @@ int rt_b200_destroy(rt_b200_ctx *c)
     cudaFree(c->d_cubic);
     cudaFree(c->d_coef_full);
     cudaFree(c->d_material);
+    cudaFree(c->d_material_pi);
     cudaFree(c->d_orig);
     cudaFree(c->d_lights);
     cudaFree(c->d_counters);
@@ -1043,8 +996,6 @@ int rt_b200_destroy(rt_b200_ctx *c)
     cudaFree(c->d_cubic_mask);
     cudaFree(c->d_grid_cells);
     cudaFree(c->d_grid_items);
-    cudaFree(c->qtables.tables);
-    delete c->qscene;
     if (c->ev_start) cudaEventDestroy(c->ev_start);
     if (c->ev_render) cudaEventDestroy(c->ev_render);
     if (c->ev_end) cudaEventDestroy(c->ev_end);
@@ -1103,7 +1054,7 @@ int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
 {
     if (!c || !name) return fail(RT_B200_ERR_ARG, "null argument");
     if (!std::strcmp(name, "kernel")) {
-        if (value < 0 || value > 2) return fail(RT_B200_ERR_ARG, "kernel must be 0, 1 or 2");
+        if (value < 0 || value > 1) return fail(RT_B200_ERR_ARG, "kernel must be 0 or 1");
         c->kernel_kind = (int) value;
     }
     else if (!std::strcmp(name, "strip_rows")) {
@@ -1114,12 +1065,8 @@ int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
         }
     }
     else if (!std::strcmp(name, "variant")) {
-        if (value != 0 && value != 2 && value != 3 && value != 5) return fail(RT_B200_ERR_ARG, "variant must be 0, 2, 3 or 5");
+        if (value < 0 || value > 64) return fail(RT_B200_ERR_ARG, "variant out of range (see rt_wave_kernel.inl: RT_WAVE_VARIANTS)");
         c->wave_variant = (int) value;
-    }
-    else if (!std::strcmp(name, "queue_variant")) {
-        if (value < 0 || value > 5) return fail(RT_B200_ERR_ARG, "queue_variant must be 0..5");
-        c->queue_variant = (int) value;
     }
     else if (!std::strcmp(name, "shadow_cache")) {
         if (value < -1 || value > 1) return fail(RT_B200_ERR_ARG, "shadow_cache must be -1, 0 or 1");
@@ -1194,7 +1141,6 @@ int rt_b200_get_launches(rt_b200_ctx *c, uint32_t *launches)
 {
     if (!c || !launches) return fail(RT_B200_ERR_ARG, "null argument");
     uint32_t n = (uint32_t) c->launches;
-    if (c->kernel_kind == 2 && c->qscene && c->view.n_sphere > 0) n += 1;   // primary-ray table
     if (c->world > 1 && c->comm && !c->shared_ready) n += 1;                 // strip un-interleave
     if (c->world > 1 && c->comm && c->shared_ready && c->flag_barrier) n += c->rank == 0 ? 3 : 2;   // sequence words
     *launches = n;

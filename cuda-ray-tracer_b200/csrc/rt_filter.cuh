@@ -80,10 +80,9 @@ __device__ __forceinline__ float sphere_slack(const RayF &r, const float4 s)
 
 // Outcome of the filter for one sphere {cx, cy, cz, r^2}.
 //   true  -> provably no intersection usable by the caller: no real root, or both roots behind the origin,
-//            or (when max_t_is_one) both roots beyond t = 1 — the exact test would not have produced a hit/occluder
+//            or (when segment01: the caller's max_t is 1, a point light's shadow ray) both roots beyond t = 1 — the exact test would not have produced a hit/occluder
 //   false -> undecided: run the exact FP64 test
-template <bool SEGMENT01>
-__device__ __forceinline__ bool sphere_rejected(const RayF &r, const float4 s)
+__device__ __forceinline__ bool sphere_rejected(const RayF &r, const float4 s, bool segment01)
 {
     const float ocx = r.ox - s.x, ocy = r.oy - s.y, ocz = r.oz - s.z;
     const float b = fmaf(ocx, r.dx, fmaf(ocy, r.dy, ocz * r.dz));
@@ -96,7 +95,7 @@ __device__ __forceinline__ bool sphere_rejected(const RayF &r, const float4 s)
     const float eb = fmaf(q2, r.kb1, r.kb0);
     const float ec = fmaf(q2, r.kc1, r.kc0);
     if (b > eb && c > ec) return true;         // origin outside, centre behind: both roots negative
-    if (SEGMENT01) {
+    if (segment01) {
         // both roots > 1  <=>  p(1) = A + 2b + c > 0 and the vertex -b/A > 1, with margins
         const float p1 = r.A + 2.0f * b + c;
         const float e1 = 2.0f * eb + ec + 4.0f * RT_U32F * (r.A + 2.0f * fabsf(b) + fabsf(c)) + 4.0f * RT_U32F * r.A;

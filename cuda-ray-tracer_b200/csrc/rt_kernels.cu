@@ -150,10 +150,4 @@ cudaError_t launch_sync_wait(const unsigned *words, int first, int n, unsigned n
     return cudaGetLastError();
 }
 
-int render_launch_count(int kernel_kind)
-{
-    (void) kernel_kind;
-    return 1;
-}
-
 } // namespace rt

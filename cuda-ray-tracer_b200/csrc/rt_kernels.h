@@ -25,33 +25,6 @@ struct WaveLaunch {
 };
 cudaError_t launch_render_wave(const SceneView &scene, const FrameParams &frame, const WaveLaunch &wl, cudaStream_t stream);
 
-// Queue kernel (rt_queue.cu): per-scene / per-frame FP32 sphere tables (rt_tables.cuh), the scene block that
-// travels in the kernel parameters (rt_queue.cuh), and the launcher.
-struct LightFilter;
-struct QueueScene;
-struct QueueTables {
-    float4 *tables;              // device, [2 + n_lights][n_sphere_pad]: 0 generic, 1 primary (per frame), 2 + j light j
-    int n_sphere_pad;            // n_sphere rounded up to a multiple of 4
-    int tables_safe;             // all sphere / light coordinates small enough for FP32 tables
-    float r_max, r2_max, center_norm_max;
-};
-struct QueueLaunch {
-    unsigned long long *tile_counter;
-    QueueTables tables;
-    const QueueScene *scene;            // host; planes, quadrics, cubics, lights and light families
-    int primary_safe;                   // camera origin small enough for the FP32 primary table
-    int shadow_cache;                   // 1 / 0 / -1 = automatic
-    int variant;                        // 0 = automatic; 1: 256 threads, tables resident; 2: 512 threads, streamed;
-                                        // 3: 512 threads, resident; 4: 256 threads, streamed
-};
-// True when planes / quadrics / cubics / lights fit the kernel-parameter block; otherwise use the wavefront kernel.
-bool queue_scene_fits(const SceneView &scene);
-LightFilter make_light_filter(const LightDev &light);
-// Rows [row_begin, row_end) of the table set; `pivot` = camera origin (used by row 1 only).
-cudaError_t build_queue_tables(const SceneView &scene, const QueueTables &qt, const QueueScene &qs, int row_begin,
-                               int row_end, const double pivot[3], cudaStream_t stream);
-cudaError_t launch_render_queue(const SceneView &scene, const FrameParams &frame, const QueueLaunch &ql, cudaStream_t stream);
-
 // Undo the strip interleave after the all-gather: gathered = [world][local_rows][width] -> frame[height][width].
 cudaError_t launch_unpack_strips(const uchar4 *gathered, uchar4 *frame, int width, int height, int strip_rows,
                                  int world, int local_rows, cudaStream_t stream);
@@ -59,9 +32,6 @@ cudaError_t launch_unpack_strips(const uchar4 *gathered, uchar4 *frame, int widt
 // Fused-gather signalling through sequence words in peer-mapped memory (rt_kernels.cu).
 cudaError_t launch_sync_store(unsigned *word, unsigned value, cudaStream_t stream);
 cudaError_t launch_sync_wait(const unsigned *words, int first, int n, unsigned need, unsigned *timed_out, cudaStream_t stream);
-
-// Number of kernels a call to launch_render_* enqueues (for bench.py's gpu_launches accounting).
-int render_launch_count(int kernel_kind);
 
 } // namespace rt
 #endif

@@ -45,6 +45,8 @@ struct SceneView {
     const int *orig_index;    // [n_objects]  class-sorted slot -> original object index
     const double *coef_full;  // [n_objects][20] by ORIGINAL index (normal_vector at the hit)
     const float4 *material;   // [n_objects] by ORIGINAL index {reflection_ratio, r, g, b}
+    const float4 *material_pi;   // [n_objects] {reflection_ratio, r / pi, g / pi, b / pi}: light_impl.h:43 divides the
+                                 // object colour by pi for every light; the wavefront kernel reads the quotients
     const LightDev *lights;   // [n_lights]
     float sphere_center_max;  // max |coordinate| over all sphere centres (FP32 filter error bound)
     SphereGrid grid;          // uniform grid over the sphere class (rt_grid.cuh); cell_start == nullptr: none

@@ -49,7 +49,7 @@ __device__ __forceinline__ void consider_lazy(Hit &h, double t, int slot, const 
     }
 }
 
-// The same rule on two scalars (queue kernel).
+// The same rule on two scalars (grid walk visitors).
 __device__ __forceinline__ void consider_lazy_t(double &best_t, int &best_slot, double t, int slot,
                                                 const int *__restrict__ orig_index)
 {

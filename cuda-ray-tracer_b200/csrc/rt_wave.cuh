@@ -12,6 +12,17 @@ namespace rt {
 constexpr int LIGHT_CHUNK = 32;  // lights handled per visibility word
 constexpr int MAX_WARPS = 16;    // largest CTA: 512 threads
 
+// Pixel tile of a W-thread CTA: every warp owns an 8x4 sub-tile (coherent rays; each warp writes four fully used
+// 32-byte sectors); up to four warps sit side by side, further warps stack upwards.
+template <int W>
+struct TileGeom {
+    static constexpr int WARPS = W / 32;
+    static constexpr int WX = WARPS >= 4 ? 4 : WARPS;
+    static constexpr int WY = WARPS / WX;
+    static constexpr int TILE_W = 8 * WX;
+    static constexpr int TILE_ROWS = 4 * WY;
+};
+
 // Scene arrays staged once per CTA into shared memory (SoA by class, rt_scene.h).
 struct SceneSmem {
     const double4 *plane;

@@ -3,6 +3,8 @@
 #ifndef RT_WAVE_DEVICE_CUH
 #define RT_WAVE_DEVICE_CUH
 
+#include <atomic>
+
 #include "rt_kernels.h"
 #include "rt_wave.cuh"
 
@@ -28,7 +30,7 @@ struct GridNearestVisitor {
     __device__ __forceinline__ bool test(int j)
     {
         r.tests++;
-        if (!rf.safe || !sphere_rejected<false>(rf, __ldg(&g.sphere_f[j]))) {
+        if (!rf.safe || !sphere_rejected(rf, __ldg(&g.sphere_f[j]), false)) {
             r.confirms++;
             consider_lazy_t(r.t, r.slot, intersect_sphere(g.sphere[j], o, d), g.n_plane + j, g.orig_index);
         }
@@ -37,18 +39,18 @@ struct GridNearestVisitor {
     __device__ __forceinline__ double bound() const { return r.t; }
 };
 
-template <bool SEGMENT01>
 struct GridOccluderVisitor {
     const SceneView &g;
     const RayF &rf;
     const d3 &o, &d;
     double max_t;
+    bool segment01;
     int found;
     unsigned confirms, tests;
     __device__ __forceinline__ bool test(int j)
     {
         tests++;
-        if (!rf.safe || !sphere_rejected<SEGMENT01>(rf, __ldg(&g.sphere_f[j]))) {
+        if (!rf.safe || !sphere_rejected(rf, __ldg(&g.sphere_f[j]), segment01)) {
             confirms++;
             if (blocks(intersect_sphere(g.sphere[j], o, d), max_t)) {
                 found = g.n_plane + j;
@@ -75,12 +77,11 @@ struct GridOccluderResult {
     unsigned confirms, tests;
 };
 
-template <bool SEGMENT01>
 static __device__ __noinline__ GridOccluderResult occluder_spheres_grid(const SceneView &g, float sphere_r2_max, d3 o, d3 d,
-                                                                        double max_t)
+                                                                        double max_t, bool segment01)
 {
     const RayF rf = make_rayf(o, d, g.sphere_center_max, sphere_r2_max);
-    GridOccluderVisitor<SEGMENT01> v{g, rf, o, d, max_t, -1, 0u, 0u};
+    GridOccluderVisitor v{g, rf, o, d, max_t, segment01, -1, 0u, 0u};
     grid_walk(g.grid, o.x, o.y, o.z, d.x, d.y, d.z, max_t, v);
     return GridOccluderResult{v.found, v.confirms, v.tests};
 }
@@ -118,7 +119,7 @@ __device__ __forceinline__ Hit nearest_hit_wave(const SceneView &g, const SceneS
             if (!(fmaxf(fmaxf(s0, s1), fmaxf(s2, s3)) < 0.0f)) {
 #pragma unroll 1
                 for (int j = i; j < i + 4; j++) {
-                    if (!sphere_rejected<false>(rf, s.sphere_f[j])) {
+                    if (!sphere_rejected(rf, s.sphere_f[j], false)) {
                         confirms++;
                         consider_lazy(h, intersect_sphere(g.sphere[j], o, d), slot + j, g.orig_index);
                     }
@@ -126,7 +127,7 @@ __device__ __forceinline__ Hit nearest_hit_wave(const SceneView &g, const SceneS
             }
         }
         for (; i < g.n_sphere; i++) {
-            if (!rf.safe || !sphere_rejected<false>(rf, s.sphere_f[i])) {
+            if (!rf.safe || !sphere_rejected(rf, s.sphere_f[i], false)) {
                 confirms++;
                 consider_lazy(h, intersect_sphere(g.sphere[i], o, d), slot + i, g.orig_index);
             }
@@ -173,8 +174,7 @@ __device__ __forceinline__ Hit nearest_hit_wave(const SceneView &g, const SceneS
     return h;
 }
 
-// exact test of one class-sorted slot (shadow cache probe)
-template <bool CUBIC>
+// exact test of one class-sorted slot (shadow cache probe; planes, spheres and quadrics)
 __device__ __forceinline__ double intersect_slot(const SceneView &g, const SceneSmem &s, int slot, const d3 &o,
                                                  const d3 &d, Tally &tl)
 {
@@ -193,23 +193,22 @@ __device__ __forceinline__ double intersect_slot(const SceneView &g, const Scene
         tl.n[CNT_T_QUADRIC]++;
         return intersect_quadric(s.quadric + 10 * slot, o, d);
     }
-    slot -= g.n_quadric;
-    if (!CUBIC) return -1.0;
-    tl.n[CNT_T_CUBIC]++;
-    tl.n[CNT_CUBIC_EXACT]++;
-    return intersect_cubic_masked(s.cubic + 20 * slot, s.cubic_mask[slot], o, d);
+    return -1.0;   // cubic slots are never cached (phase C): one copy less of the exact cubic test in the kernel
 }
 
 // ---- phase C: any occluder with EPS < t < max_t (update-cpu.cpp:66-72); returns the occluding slot or -1 ----
 // The boolean is order-independent, so classes are visited cheapest-first, except that the cubic class moves
 // in front of the sphere class while cubics are the more productive occluders per unit of work (block-local
 // statistics in WaveCtl::occ_found, updated as occluders are found).
-template <bool SEGMENT01, bool GRID>
+// Code size matters here (the kernel's instruction footprint was 27 400 SASS instructions in round 1, two thirds of it
+// copies of these searches, and "no instruction" the top stall on dingdong): every class search below exists ONCE —
+// the point-light / directional distinction (segment01) is a run-time flag and the sphere / cubic order a two-pass loop.
+template <bool GRID>
 __device__ __forceinline__ int occluder_spheres(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg,
-                                                const d3 &o, const d3 &d, double max_t, Tally &tl)
+                                                const d3 &o, const d3 &d, double max_t, bool segment01, Tally &tl)
 {
     if (GRID && cfg.use_grid && grid_ray_ok(g.grid, o.x, o.y, o.z, d.x, d.y, d.z)) {
-        const GridOccluderResult r = occluder_spheres_grid<SEGMENT01>(g, cfg.sphere_r2_max, o, d, max_t);
+        const GridOccluderResult r = occluder_spheres_grid(g, cfg.sphere_r2_max, o, d, max_t, segment01);
         tl.n[CNT_T_SPHERE] += r.tests;
         tl.n[CNT_CONFIRM] += r.confirms;
         return r.found;
@@ -225,7 +224,7 @@ __device__ __forceinline__ int occluder_spheres(const SceneView &g, const SceneS
         if (!(fmaxf(fmaxf(s0, s1), fmaxf(s2, s3)) < 0.0f)) {
 #pragma unroll 1
             for (int j = i; j < i + 4; j++) {
-                if (!sphere_rejected<SEGMENT01>(rf, s.sphere_f[j])) {
+                if (!sphere_rejected(rf, s.sphere_f[j], segment01)) {
                     tl.n[CNT_CONFIRM]++;
                     if (blocks(intersect_sphere(g.sphere[j], o, d), max_t)) {
                         found = slot + j;
@@ -235,8 +234,9 @@ __device__ __forceinline__ int occluder_spheres(const SceneView &g, const SceneS
             }
         }
     }
+#pragma unroll 1
     for (; i < g.n_sphere && found < 0; i++) {
-        if (!rf.safe || !sphere_rejected<SEGMENT01>(rf, s.sphere_f[i])) {
+        if (!rf.safe || !sphere_rejected(rf, s.sphere_f[i], segment01)) {
             tl.n[CNT_CONFIRM]++;
             if (blocks(intersect_sphere(g.sphere[i], o, d), max_t)) found = slot + i;
         }
@@ -245,30 +245,26 @@ __device__ __forceinline__ int occluder_spheres(const SceneView &g, const SceneS
     return found;
 }
 
-// hit_slot / light: wave slot of the hit this shadow ray starts from and index of the light it goes to, the keys of
-// the filter caches (SceneSmem::hit_o, light_d) that exist when the scene has exactly one cubic.
+// Cubic class.  hit_slot / light: wave slot of the hit this shadow ray starts from and index of the light it goes to,
+// the keys of the filter caches (SceneSmem::hit_o, light_d) that exist when the scene has exactly one cubic: the origin
+// half of the FP32 expansion per hit, the direction half per directional light (a point light's direction differs per
+// hit).  One verdict call site and one exact test for both the cached and the generic form.
 __device__ __forceinline__ int occluder_cubics(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg, const d3 &o,
-                                               const d3 &d, double max_t, int hit_slot, int light, Tally &tl)
+                                               const d3 &d, double max_t, bool segment01, int hit_slot, int light, Tally &tl)
 {
     const int base = g.n_plane + g.n_sphere + g.n_quadric;
-    const float hi = (float) max_t;   // 1 or 1e6, both exact in FP32
-    const float dfx = (float) d.x, dfy = (float) d.y, dfz = (float) d.z;
-    if (cfg.use_cubic_filter && s.hit_o) {
-        tl.n[CNT_T_CUBIC]++;
-        // point light: the direction differs per hit; directional light: cached per light
-        const CubicD cd = (hi == 1.0f) ? make_cubic_d(s.cubic_f, dfx, dfy, dfz) : s.light_d[light];
-        const int v = cubic_verdict_od(s.hit_o[hit_slot], cd, hi, true);
-        if (v == CV_MISS) return -1;
-        if (v == CV_HIT) return base;
-        tl.n[CNT_CUBIC_EXACT]++;
-        return blocks(intersect_cubic_masked(s.cubic, s.cubic_mask[0], o, d), max_t) ? base : -1;
-    }
+    const float hi = segment01 ? 1.0f : (float) RT_MAX_T;   // = max_t, exact in FP32
     const float ofx = (float) o.x, ofy = (float) o.y, ofz = (float) o.z;
+    const float dfx = (float) d.x, dfy = (float) d.y, dfz = (float) d.z;
+    const bool cached = s.hit_o != nullptr;
+#pragma unroll 1
     for (int i = 0; i < g.n_cubic; i++) {
         tl.n[CNT_T_CUBIC]++;
         if (cfg.use_cubic_filter) {
             const float *kf = s.cubic_f + RT_CF_FLOATS * i;
-            const int v = cubic_verdict_od(make_cubic_o(kf, ofx, ofy, ofz), make_cubic_d(kf, dfx, dfy, dfz), hi, true);
+            const CubicO co = cached ? s.hit_o[hit_slot] : make_cubic_o(kf, ofx, ofy, ofz);
+            const CubicD cd = (cached && !segment01) ? s.light_d[light] : make_cubic_d(kf, dfx, dfy, dfz);
+            const int v = cubic_verdict_od(co, cd, hi, true);
             if (v == CV_MISS) continue;
             if (v == CV_HIT) return base + i;
         }
@@ -278,9 +274,9 @@ __device__ __forceinline__ int occluder_cubics(const SceneView &g, const SceneSm
     return -1;
 }
 
-template <bool SEGMENT01, bool CUBIC, bool GRID>
+template <bool CUBIC, bool GRID>
 __device__ __forceinline__ int occluder_wave(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg, WaveCtl &ctl,
-                                             const d3 &o, const d3 &d, double max_t, int hit_slot, int light, Tally &tl)
+                                             const d3 &o, const d3 &d, double max_t, bool segment01, int hit_slot, int light, Tally &tl)
 {
     for (int i = 0; i < g.n_plane; i++) {
         tl.n[CNT_T_PLANE]++;
@@ -291,21 +287,31 @@ __device__ __forceinline__ int occluder_wave(const SceneView &g, const SceneSmem
         tl.n[CNT_T_QUADRIC]++;
         if (blocks(intersect_quadric(s.quadric + 10 * i, o, d), max_t)) return quad_base + i;
     }
-    if (g.n_sphere == 0) return (CUBIC && g.n_cubic) ? occluder_cubics(g, s, cfg, o, d, max_t, hit_slot, light, tl) : -1;
-    if (!CUBIC || g.n_cubic == 0) return occluder_spheres<SEGMENT01, GRID>(g, s, cfg, o, d, max_t, tl);
-    // relative cost of a full pass: ~4 issue slots x 4 per sphere filter (a flat ~2000 for a grid walk), ~600 per exact
-    // cubic test
-    const volatile int *found = ctl.occ_found;
-    const long long sphere_pass = (GRID && cfg.use_grid) ? 2000LL : 16LL * g.n_sphere;
-    const bool cubic_first = (long long) found[1] * sphere_pass > (long long) found[0] * (600LL * g.n_cubic);
-    int by = cubic_first ? occluder_cubics(g, s, cfg, o, d, max_t, hit_slot, light, tl) : occluder_spheres<SEGMENT01, GRID>(g, s, cfg, o, d, max_t, tl);
-    if (by >= 0) {
-        atomicAdd(&ctl.occ_found[cubic_first ? 1 : 0], 1);
-        return by;
+    const bool have_s = g.n_sphere > 0, have_c = CUBIC && g.n_cubic > 0;
+    bool cubic_first = !have_s;
+    if (have_s && have_c) {
+        // relative cost of a full pass: ~4 issue slots x 4 per sphere filter (a flat ~2000 for a grid walk), ~600 per
+        // exact cubic test
+        const volatile int *found = ctl.occ_found;
+        const long long sphere_pass = (GRID && cfg.use_grid) ? 2000LL : 16LL * g.n_sphere;
+        cubic_first = (long long) found[1] * sphere_pass > (long long) found[0] * (600LL * g.n_cubic);
     }
-    by = cubic_first ? occluder_spheres<SEGMENT01, GRID>(g, s, cfg, o, d, max_t, tl) : occluder_cubics(g, s, cfg, o, d, max_t, hit_slot, light, tl);
-    if (by >= 0) atomicAdd(&ctl.occ_found[cubic_first ? 0 : 1], 1);
-    return by;
+#pragma unroll 1
+    for (int pass = 0; pass < 2; pass++) {
+        const bool cubics_now = (pass == 0) == cubic_first;
+        int by = -1;
+        if (cubics_now) {
+            if (have_c) by = occluder_cubics(g, s, cfg, o, d, max_t, segment01, hit_slot, light, tl);
+        }
+        else if (have_s) {
+            by = occluder_spheres<GRID>(g, s, cfg, o, d, max_t, segment01, tl);
+        }
+        if (by >= 0) {
+            if (have_s && have_c) atomicAdd(&ctl.occ_found[cubics_now ? 1 : 0], 1);
+            return by;
+        }
+    }
+    return -1;
 }
 
 } // namespace

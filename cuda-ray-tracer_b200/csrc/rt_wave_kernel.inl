@@ -33,7 +33,9 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int WAVE = W;
-    constexpr int TILE_ROWS = W / 32;            // tile = 32 x TILE_ROWS pixels, an 8x4 sub-tile per warp
+    constexpr int WX = TileGeom<W>::WX;              // warps side by side in a tile, an 8x4 sub-tile per warp
+    constexpr int TILE_W = TileGeom<W>::TILE_W;      // tile = TILE_W x TILE_ROWS pixels
+    constexpr int TILE_ROWS = TileGeom<W>::TILE_ROWS;
     Pool<W> &pool = *reinterpret_cast<Pool<W> *>(smem_raw);
     WaveHits<W> &wh = *reinterpret_cast<WaveHits<W> *>(smem_raw + align16(sizeof(Pool<W>)));
     WaveCtl &ctl = *reinterpret_cast<WaveCtl *>(smem_raw + align16(sizeof(Pool<W>)) + align16(sizeof(WaveHits<W>)));
@@ -156,15 +158,15 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
             if (!tiles_left) break;
             continue;   // unreachable in practice: tile < 0 with tiles_left means pool >= WAVE
         }
-        if (tile >= 0 && tid < 32 + TILE_ROWS) {
+        if (tile >= 0 && tid < TILE_W + TILE_ROWS) {
             // the two divisions of primary ray generation (update-cpu.cpp:84-87) once per column / row of the tile
             const int tx = tile % cfg.tiles_x, ty = tile / cfg.tiles_x;
-            if (tid < 32) {
-                ctl.cam_x[tid] = primary_cam_x(f, tx * 32 + tid);
+            if (tid < TILE_W) {
+                ctl.cam_x[tid] = primary_cam_x(f, tx * TILE_W + tid);
             }
             else {
-                const int lrow = f.row0 + ty * TILE_ROWS + (tid - 32);
-                ctl.cam_y[tid - 32] = primary_cam_y(f, local_to_image_row(lrow, f.strip_rows, f.rank, f.world));
+                const int lrow = f.row0 + ty * TILE_ROWS + (tid - TILE_W);
+                ctl.cam_y[tid - TILE_W] = primary_cam_y(f, local_to_image_row(lrow, f.strip_rows, f.rank, f.world));
             }
         }
         __syncthreads();   // everyone has read ctl.tile / pool_count before they change
@@ -177,8 +179,8 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         const bool primary = tile >= 0;
         if (primary) {
             const int tx = tile % cfg.tiles_x, ty = tile / cfg.tiles_x;
-            const int x = tx * 32 + (warp & 3) * 8 + (lane & 7);
-            const int lrow = f.row0 + ty * TILE_ROWS + (warp >> 2) * 4 + (lane >> 3);
+            const int x = tx * TILE_W + (warp % WX) * 8 + (lane & 7);
+            const int lrow = f.row0 + ty * TILE_ROWS + (warp / WX) * 4 + (lane >> 3);
             const int y = local_to_image_row(lrow, f.strip_rows, f.rank, f.world);
             const bool in_buf = x < f.width && lrow < f.row0 + f.rows && lrow < f.local_rows;
             active = in_buf && y < f.height;
@@ -186,7 +188,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
             if (in_buf && !active && !f.direct) f.out[pixel] = make_uchar4(0, 0, 0, 0);   // padding row past the image
             if (active) {
                 o = cam_origin;
-                d = primary_dir_cam(f, cam_origin, ctl.cam_x[(warp & 3) * 8 + (lane & 7)], ctl.cam_y[(warp >> 2) * 4 + (lane >> 3)]);
+                d = primary_dir_cam(f, cam_origin, ctl.cam_x[(warp % WX) * 8 + (lane & 7)], ctl.cam_y[(warp / WX) * 4 + (lane >> 3)]);
                 if (COUNT) tl.n[CNT_PRIMARY]++;
             }
         }
@@ -256,7 +258,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         // ---- phases C + D per chunk of 32 lights ---------------------------------------------------------------
         float acc_r = 0.f, acc_g = 0.f, acc_b = 0.f;
         float4 mat = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (hit) mat = __ldg(&g.material[obj]);
+        if (hit) mat = __ldg(&g.material_pi[obj]);   // {reflection_ratio, colour / pi}
         for (int l0 = 0; l0 < g.n_lights; l0 += LIGHT_CHUNK) {
             const int lc = min(LIGHT_CHUNK, g.n_lights - l0);
             if (l0 > 0) {   // first chunk: cleared with the hit record, before the barrier that published the records
@@ -264,8 +266,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
                 __syncthreads();
             }
             // C: task = (light j, hit i), light-major
-            const unsigned inv_hits = n_hits > 1 ? (unsigned) ((0x100000000ULL + n_hits - 1) / (unsigned) n_hits) : 0u;   // ceil(2^32 / n)
-            const bool lone_cubic = CUBIC && s.hit_o != nullptr && cfg.use_cubic_filter && g.n_objects == 1;
+            const unsigned inv_hits = n_hits > 1 ? 0xffffffffu / (unsigned) n_hits + 1u : 0u;   // ceil(2^32 / n), 32-bit division
             for (int task = tid; task < n_hits * lc; task += WAVE) {
                 const int j = n_hits > 1 ? (int) __umulhi((unsigned) task, inv_hits) : task;   // task / n_hits (task * n_hits < 2^32)
                 const int k = wh.hitlist[task - j * n_hits];
@@ -277,37 +278,19 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
                     continue;
                 }
                 if (COUNT) tl.n[CNT_SHADOW]++;
+                const d3 so = d3{p.x + RT_SHADOW_BIAS * n.x, p.y + RT_SHADOW_BIAS * n.y, p.z + RT_SHADOW_BIAS * n.z};
+                double max_t;
+                const d3 sd = shadow_dir(l, p, max_t);
                 bool occ = false;
-                int verdict = CV_UNKNOWN;
-                if (lone_cubic) {
-                    // the only object is one cubic: the cached filter halves decide most shadow rays without
-                    // touching FP64 (rt_cubic_filter.cuh); the exact path below runs for the undecided ones
-                    if (COUNT) tl.n[CNT_T_CUBIC]++;
-                    const CubicD cd = l.is_spherical ? make_cubic_d(s.cubic_f, (float) (l.px - p.x), (float) (l.py - p.y), (float) (l.pz - p.z))
-                                                     : s.light_d[l0 + j];
-                    verdict = cubic_verdict_od(s.hit_o[k], cd, l.is_spherical ? 1.0f : (float) RT_MAX_T, true);
-                    occ = verdict == CV_HIT;
+                if (cfg.use_shadow_cache) {
+                    const int cs = ctl.shadow_cache[j];
+                    if (cs >= 0) occ = blocks(intersect_slot(g, s, cs, so, sd, tl), max_t);
                 }
-                if (verdict == CV_UNKNOWN) {
-                    const d3 so = d3{p.x + RT_SHADOW_BIAS * n.x, p.y + RT_SHADOW_BIAS * n.y, p.z + RT_SHADOW_BIAS * n.z};
-                    double max_t;
-                    const d3 sd = shadow_dir(l, p, max_t);
-                    if (lone_cubic) {
-                        if (COUNT) tl.n[CNT_CUBIC_EXACT]++;
-                        occ = blocks(intersect_cubic_masked(s.cubic, s.cubic_mask[0], so, sd), max_t);
-                    }
-                    else {
-                        if (cfg.use_shadow_cache) {
-                            const int cs = ctl.shadow_cache[j];
-                            if (cs >= 0) occ = blocks(intersect_slot<CUBIC>(g, s, cs, so, sd, tl), max_t);
-                        }
-                        if (!occ) {
-                            const int by = l.is_spherical ? occluder_wave<true, CUBIC, GRID>(g, s, cfg, ctl, so, sd, max_t, k, l0 + j, tl)
-                                                          : occluder_wave<false, CUBIC, GRID>(g, s, cfg, ctl, so, sd, max_t, k, l0 + j, tl);
-                            occ = by >= 0;
-                            if (occ && cfg.use_shadow_cache) ctl.shadow_cache[j] = by;   // benign race: any occluder will do
-                        }
-                    }
+                if (!occ) {
+                    const int by = occluder_wave<CUBIC, GRID>(g, s, cfg, ctl, so, sd, max_t, l.is_spherical != 0, k, l0 + j, tl);
+                    occ = by >= 0;
+                    // benign race: any occluder will do; cubic slots are not cached (intersect_slot does not probe them)
+                    if (occ && cfg.use_shadow_cache && by < g.n_plane + g.n_sphere + g.n_quadric) ctl.shadow_cache[j] = by;
                 }
                 if (occ) atomicOr(&wh.occluded[k], 1u << j);
             }
@@ -321,7 +304,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
                 const float3 oc = make_float3(mat.y, mat.z, mat.w);
                 for (int j = 0; j < lc; j++) {
                     if (!((occ >> j) & 1u)) {
-                        shade_light(s.lights[l0 + j], p, n, oc, acc);
+                        shade_light_pi(s.lights[l0 + j], p, n, oc, acc);
                         if (COUNT) tl.n[CNT_LIT]++;
                     }
                 }
@@ -421,18 +404,22 @@ template <int W, int MINB, bool CUBIC, bool GRID = false>
 cudaError_t launch_wave_variant(const SceneView &scene, const FrameParams &frame, WaveConfig cfg, size_t scene_smem,
                                 int n_sm, int max_smem, cudaStream_t stream)
 {
-    static bool attr_set = false;
+    static std::atomic<unsigned long long> attr_set{0ULL};   // bit d: the attribute is set on device d (it is per device)
     auto kern = frame.counters ? render_wave_kernel<W, MINB, true, CUBIC, GRID> : render_wave_kernel<W, MINB, false, CUBIC, GRID>;
     cudaError_t e;
-    if (!attr_set) {
+    int dev = 0;
+    e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    // Setting it twice from two threads is harmless; devices past 63 set it on every launch.
+    if (dev >= 64 || !((attr_set.load(std::memory_order_acquire) >> dev) & 1ULL)) {
         e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, true, CUBIC, GRID>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, false, CUBIC, GRID>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
         if (e != cudaSuccess) return e;
-        attr_set = true;
+        if (dev < 64) attr_set.fetch_or(1ULL << dev, std::memory_order_release);
     }
     const size_t smem = wave_fixed_smem<W>() + scene_smem + wave_cubic_smem(scene, W);
-    cfg.tiles_x = (frame.width + 31) / 32;
-    cfg.tiles_y = (frame.rows + W / 32 - 1) / (W / 32);
+    cfg.tiles_x = (frame.width + TileGeom<W>::TILE_W - 1) / TileGeom<W>::TILE_W;
+    cfg.tiles_y = (frame.rows + TileGeom<W>::TILE_ROWS - 1) / TileGeom<W>::TILE_ROWS;
     int per_sm = 1;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W, smem);
     if (e != cudaSuccess) return e;
@@ -444,9 +431,12 @@ cudaError_t launch_wave_variant(const SceneView &scene, const FrameParams &frame
     return cudaGetLastError();
 }
 
-// Variant choice: 256-thread CTAs, three per SM, while the staged scene leaves room for that; otherwise one
-// 512-thread CTA per SM so that a large scene is staged once and still 16 warps are resident.  (256 x {1, 4} were
-// measured in round 1 and never won; they are no longer compiled.)
+// Variants (option "variant"): code -> (threads per CTA, CTAs per SM the register budget is cut for).
+//   2: 256 x 2 (128 registers)   3: 256 x 3 (80 registers)   5: 512 x 1 (128 registers)
+// Smaller CTAs at the same 24 warps per SM (128 x 6, 64 x 12, 32 x 24; 128 x 4, 64 x 8, 32 x 16 at 128 registers) were
+// measured in round 2 (profiles/r2_a_variants.jsonl): slower on every bundled scene but quadratic / reflection_test
+// (128 x 6: -2 %), so barriers are not what limits the kernel; they are not compiled.
+#define RT_WAVE_VARIANTS(X) X(2, 256, 2) X(3, 256, 3) X(5, 512, 1)
 } // namespace
 
 // The kernels with the grid walk are instantiated in their own translation units (rt_wave_grid.cu with the cubic class,
@@ -507,9 +497,10 @@ cudaError_t launch_render_wave_t(const SceneView &scene, const FrameParams &fram
     int variant = wl.variant;
     if (variant <= 0) variant = (3 * cta256 <= (size_t) sm_smem) ? 3 : 5;
     switch (variant) {
-        case 2: return launch_wave_variant<256, 2, CUBIC>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
-        case 3: return launch_wave_variant<256, 3, CUBIC>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
-        case 5: return launch_wave_variant<512, 1, CUBIC>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
+#define RT_WAVE_CASE(CODE, THREADS, MINB) \
+        case CODE: return launch_wave_variant<THREADS, MINB, CUBIC>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
+        RT_WAVE_VARIANTS(RT_WAVE_CASE)
+#undef RT_WAVE_CASE
         default: return cudaErrorInvalidValue;
     }
 }

@@ -21,6 +21,8 @@ ap.add_argument("--height", type=int, default=2160)
 ap.add_argument("--bounces", type=int, default=4)
 ap.add_argument("--pose", default="initial")
 ap.add_argument("--accel", type=int, default=-1)
+ap.add_argument("--count", type=int, default=0, help="1 = the counting instantiation of the kernel")
+ap.add_argument("--option", action="append", default=[], help="name=value, passed to rt_b200_set_option")
 a = ap.parse_args()
 if a.scene == "synthetic":
     from cuda_ray_tracer_b200 import synth
@@ -31,6 +33,10 @@ else:
 with binding.Renderer(sc) as r:
     r.set_option("kernel", a.kernel)
     r.set_option("accel", a.accel)
+    r.set_option("count", a.count)
+    for o in a.option:
+        k, v = o.split("=")
+        r.set_option(k, int(v))
     for _ in range(a.frames):
         ms = r.update(camera.TEST_POSES[a.pose])
-    print(a.scene, "kernel", a.kernel, "last frame ms", ms, r.counters())
+    print(a.scene, "kernel", a.kernel, "last frame ms", ms, r.counters() if a.count else "")
