@@ -29,7 +29,7 @@ EXPORTS = ("rt_b200_upload_scene", "rt_b200_update", "rt_b200_gather", "rt_b200_
            "rt_b200_get_timing", "rt_b200_get_class_counts", "rt_b200_strip_layout", "rt_b200_version",
            "rt_b200_update_to_host", "rt_b200_frame_export", "rt_b200_frame_attach", "rt_b200_get_launches",
            "rt_b200_host_alloc", "rt_b200_host_free", "rt_b200_host_alloc_shared", "rt_b200_host_free_shared",
-           "rt_b200_get_grid_info", "rt_b200_band_layout")
+           "rt_b200_get_grid_info", "rt_b200_band_layout", "rt_b200_frame_attach_peer")
 
 UNIQUE_ID_BYTES = 128
 IPC_HANDLE_BYTES = 64
@@ -73,6 +73,7 @@ def load_library():
     L.rt_b200_update_to_host.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(C.c_float)]
     L.rt_b200_frame_export.argtypes = [vp, vp]
     L.rt_b200_frame_attach.argtypes = [vp, vp]
+    L.rt_b200_frame_attach_peer.argtypes = [vp, vp]
     L.rt_b200_get_launches.argtypes = [vp, C.POINTER(C.c_uint32)]
     L.rt_b200_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
     L.rt_b200_host_free.argtypes = [vp]
@@ -185,6 +186,10 @@ class Renderer:
     def frame_attach(self, handle: bytes):
         buf = C.create_string_buffer(handle, IPC_HANDLE_BYTES)
         _check(load_library().rt_b200_frame_attach(self._h, buf))
+
+    def frame_attach_peer(self, owner: "Renderer"):
+        """Same-process fused gather: `owner` is rank 0's Renderer (after frame_export), possibly on another device."""
+        _check(load_library().rt_b200_frame_attach_peer(self._h, owner._h))
 
     def launches(self) -> int:
         n = C.c_uint32()

@@ -213,6 +213,7 @@ struct rt_b200_ctx {
     uchar4 *d_shared_base = nullptr;   // rank 0: cudaMalloc; other ranks: cudaIpcOpenMemHandle
     uchar4 *d_shared[2] = {nullptr, nullptr};
     bool shared_owner = false, shared_ready = false;
+    bool shared_local = false;         // the frame belongs to another context of THIS process (peer access, no IPC, no NCCL)
     int parity = 0;
     int *d_barrier = nullptr;
     // sequence words behind the two frames in rank 0's allocation: flags[rank] = last frame this rank finished,
@@ -591,7 +592,9 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
     SharedBlock *blk = (host_sink && c->world > 1) ? find_block(host_sink) : nullptr;
     if (blk && blk->bytes < frame_bytes)
         return fail(RT_B200_ERR_ARG, "shared host block holds %zu bytes, frame needs %zu", blk->bytes, frame_bytes);
-    const bool shared = c->world > 1 && c->comm && c->shared_ready && !blk;
+    // fused gather: needs the frame attached, and either a communicator (flag_barrier = 0 uses an all-reduce) or the
+    // flag words alone (contexts of one process, rt_b200_frame_attach_peer)
+    const bool shared = c->world > 1 && c->shared_ready && !blk && (c->comm || (c->shared_local && c->flag_barrier));
     if (shared) {
         c->parity ^= 1;                 // rank 0 may still be reading the previous frame: write the other buffer
         f.out = c->d_shared[c->parity];
@@ -691,8 +694,13 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
                     // the block may still hold the frame rank 0's caller is reading: wait until rank 0 has entered
                     // this frame too (rendering is already queued, only the copies wait)
                     const double t0 = tracing ? now_seconds() : 0.0;
-                    if (!host_wait_word(&blk->trailer()->go, host_seq, 20.0))
+                    if (!host_wait_word(&blk->trailer()->go, host_seq, 20.0)) {
+                        // nothing of this frame may still be in flight when the caller gets the error
+                        cudaStreamSynchronize(c->stream);
+                        cudaStreamSynchronize(c->stream2);
+                        cudaStreamSynchronize(c->copy_stream);
                         return fail(RT_B200_ERR_STATE, "rank 0 did not enter frame %u of the shared host block (timeout)", host_seq);
+                    }
                     go_seen = true;
                     if (tracing) t_go = now_seconds() - t0;
                 }
@@ -732,7 +740,7 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
     if (blk) {
         c->last_frame = nullptr;   // the frame is assembled in host memory; rt_b200_gather would see this rank's rows only
     }
-    else if (c->world > 1 && c->comm) {
+    else if (c->world > 1 && (c->comm || shared)) {
         if (shared && c->flag_barrier) {
             // every rank's pixels are already in rank 0's frame: each rank publishes "frame seq done" in rank 0's
             // memory, and only rank 0 — the consumer of the frame — waits for all of them
@@ -769,7 +777,12 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
     CUDA_TRY(cudaEventSynchronize(c->ev_end));
     CUDA_TRY(cudaGetLastError());
     if (shared && c->flag_barrier) {
-        if (*static_cast<volatile unsigned *>(c->h_timed_out)) return fail(RT_B200_ERR_STATE, "a peer rank did not finish its part of the frame (sync timeout)");
+        if (*static_cast<volatile unsigned *>(c->h_timed_out)) {
+            // report once and re-arm: the peers may recover; nothing of this frame is still in flight (events waited above)
+            *static_cast<volatile unsigned *>(c->h_timed_out) = 0u;
+            cudaStreamSynchronize(c->stream);
+            return fail(RT_B200_ERR_STATE, "a peer rank did not finish its part of the frame (sync timeout)");
+        }
     }
     CUDA_TRY(cudaEventElapsedTime(&c->ms_render, c->ev_start, c->ev_render));
     CUDA_TRY(cudaEventElapsedTime(&c->ms_gather, c->ev_render, c->ev_end));
@@ -941,6 +954,43 @@ int rt_b200_frame_attach(rt_b200_ctx *c, const void *handle)
     return RT_B200_OK;
 }
 
+int rt_b200_frame_attach_peer(rt_b200_ctx *c, rt_b200_ctx *owner)
+{
+    if (!c || !owner) return fail(RT_B200_ERR_ARG, "null argument");
+    if (c->world < 2 || owner->world != c->world) return fail(RT_B200_ERR_ARG, "contexts of one multi-GPU job expected");
+    if (c->width != owner->width || c->height != owner->height) return fail(RT_B200_ERR_ARG, "frame sizes differ");
+    if (c->world > 1000) return fail(RT_B200_ERR_ARG, "too many ranks for the sync words");
+    const size_t px = (size_t) c->width * c->height;
+    if (c != owner) {
+        if (c->d_shared_base) return fail(RT_B200_ERR_STATE, "a shared frame is already attached");
+        if (!owner->d_shared_base || !owner->shared_owner) return fail(RT_B200_ERR_STATE, "the owner has not exported a frame (rt_b200_frame_export)");
+        CUDA_TRY(cudaSetDevice(c->device));
+        if (c->device != owner->device) {
+            int can = 0;
+            CUDA_TRY(cudaDeviceCanAccessPeer(&can, c->device, owner->device));
+            if (!can) return fail(RT_B200_ERR_CUDA, "device %d cannot access device %d's memory", c->device, owner->device);
+            const cudaError_t e = cudaDeviceEnablePeerAccess(owner->device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+                return fail(RT_B200_ERR_CUDA, "cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
+            (void) cudaGetLastError();
+        }
+        c->d_shared_base = owner->d_shared_base;
+        c->shared_local = true;
+    }
+    else {
+        if (!c->shared_owner) return fail(RT_B200_ERR_STATE, "the owner has not exported a frame (rt_b200_frame_export)");
+        CUDA_TRY(cudaSetDevice(c->device));
+        c->shared_local = true;
+    }
+    c->d_shared[0] = c->d_shared_base;
+    c->d_shared[1] = c->d_shared_base + px;
+    c->d_flags = reinterpret_cast<unsigned *>(c->d_shared_base + 2 * px);
+    c->d_go = c->d_flags + 1000;
+    c->seq = 0;
+    c->shared_ready = true;
+    return RT_B200_OK;
+}
+
 int rt_b200_gather(rt_b200_ctx *c, void *host_rgba8, size_t host_bytes, const void **device_rgba8)
 {
     if (!c) return fail(RT_B200_ERR_ARG, "null context");
@@ -1009,7 +1059,7 @@ int rt_b200_destroy(rt_b200_ctx *c)
     if (c->h_timed_out) cudaFreeHost(c->h_timed_out);
     if (c->d_shared_base) {
         if (c->shared_owner) cudaFree(c->d_shared_base);
-        else cudaIpcCloseMemHandle(c->d_shared_base);
+        else if (!c->shared_local) cudaIpcCloseMemHandle(c->d_shared_base);   // a peer pointer of this process is not ours to free
     }
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -1141,8 +1191,8 @@ int rt_b200_get_launches(rt_b200_ctx *c, uint32_t *launches)
 {
     if (!c || !launches) return fail(RT_B200_ERR_ARG, "null argument");
     uint32_t n = (uint32_t) c->launches;
-    if (c->world > 1 && c->comm && !c->shared_ready) n += 1;                 // strip un-interleave
-    if (c->world > 1 && c->comm && c->shared_ready && c->flag_barrier) n += c->rank == 0 ? 3 : 2;   // sequence words
+    if (c->world > 1 && c->comm && !c->shared_ready) n += 1;                 // strip un-interleave (the all-gather itself is NCCL's)
+    if (c->world > 1 && c->shared_ready && c->flag_barrier && !c->sync_in_kernel) n += c->rank == 0 ? 3 : 2;   // sequence-word kernels (kernel 0 only: kernel 1 does the hand-shake itself)
     *launches = n;
     return RT_B200_OK;
 }

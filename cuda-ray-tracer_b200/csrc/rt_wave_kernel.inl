@@ -267,6 +267,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
             }
             // C: task = (light j, hit i), light-major
             const unsigned inv_hits = n_hits > 1 ? 0xffffffffu / (unsigned) n_hits + 1u : 0u;   // ceil(2^32 / n), 32-bit division
+            const bool lone_cubic = CUBIC && s.hit_o != nullptr && cfg.use_cubic_filter && g.n_objects == 1;
             for (int task = tid; task < n_hits * lc; task += WAVE) {
                 const int j = n_hits > 1 ? (int) __umulhi((unsigned) task, inv_hits) : task;   // task / n_hits (task * n_hits < 2^32)
                 const int k = wh.hitlist[task - j * n_hits];
@@ -278,19 +279,38 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
                     continue;
                 }
                 if (COUNT) tl.n[CNT_SHADOW]++;
-                const d3 so = d3{p.x + RT_SHADOW_BIAS * n.x, p.y + RT_SHADOW_BIAS * n.y, p.z + RT_SHADOW_BIAS * n.z};
-                double max_t;
-                const d3 sd = shadow_dir(l, p, max_t);
                 bool occ = false;
-                if (cfg.use_shadow_cache) {
-                    const int cs = ctl.shadow_cache[j];
-                    if (cs >= 0) occ = blocks(intersect_slot(g, s, cs, so, sd, tl), max_t);
+                int verdict = CV_UNKNOWN;
+                if (lone_cubic) {
+                    // the only object is one cubic (four of the five bundled cubic scenes): the cached filter halves decide
+                    // most shadow rays without touching FP64 (rt_cubic_filter.cuh), not even for the ray's origin and
+                    // direction; the exact test below runs for the undecided ones
+                    if (COUNT) tl.n[CNT_T_CUBIC]++;
+                    const CubicD cd = l.is_spherical ? make_cubic_d(s.cubic_f, (float) (l.px - p.x), (float) (l.py - p.y), (float) (l.pz - p.z))
+                                                     : s.light_d[l0 + j];
+                    verdict = cubic_verdict_od(s.hit_o[k], cd, l.is_spherical ? 1.0f : (float) RT_MAX_T, true);
+                    occ = verdict == CV_HIT;
                 }
-                if (!occ) {
-                    const int by = occluder_wave<CUBIC, GRID>(g, s, cfg, ctl, so, sd, max_t, l.is_spherical != 0, k, l0 + j, tl);
-                    occ = by >= 0;
-                    // benign race: any occluder will do; cubic slots are not cached (intersect_slot does not probe them)
-                    if (occ && cfg.use_shadow_cache && by < g.n_plane + g.n_sphere + g.n_quadric) ctl.shadow_cache[j] = by;
+                if (verdict == CV_UNKNOWN) {
+                    const d3 so = d3{p.x + RT_SHADOW_BIAS * n.x, p.y + RT_SHADOW_BIAS * n.y, p.z + RT_SHADOW_BIAS * n.z};
+                    double max_t;
+                    const d3 sd = shadow_dir(l, p, max_t);
+                    if (lone_cubic) {
+                        if (COUNT) tl.n[CNT_CUBIC_EXACT]++;
+                        occ = blocks(intersect_cubic_masked(s.cubic, s.cubic_mask[0], so, sd), max_t);
+                    }
+                    else {
+                        if (cfg.use_shadow_cache) {
+                            const int cs = ctl.shadow_cache[j];
+                            if (cs >= 0) occ = blocks(intersect_slot(g, s, cs, so, sd, tl), max_t);
+                        }
+                        if (!occ) {
+                            const int by = occluder_wave<CUBIC, GRID>(g, s, cfg, ctl, so, sd, max_t, l.is_spherical != 0, k, l0 + j, tl);
+                            occ = by >= 0;
+                            // benign race: any occluder will do; cubic slots are not cached (intersect_slot does not probe them)
+                            if (occ && cfg.use_shadow_cache && by < g.n_plane + g.n_sphere + g.n_quadric) ctl.shadow_cache[j] = by;
+                        }
+                    }
                 }
                 if (occ) atomicOr(&wh.occluded[k], 1u << j);
             }

@@ -3,7 +3,9 @@
 //   rt_headless <scene.yml> [--width W] [--height H] [--max-reflections N]      (override the YAML values)
 //               [--frames K] [--position x,y,z] [--yaw deg] [--pitch deg]       (camera: ray-tracer.cpp:25-32)
 //               [--orbit]                                                       (scripted fly-through: yaw sweeps 60..120)
-//               [--out frame.ppm] [--raw frame.rgba] [--kernel 0|1|2]
+//               [--out frame.ppm] [--raw frame.rgba] [--kernel 0|1]
+//               [--gpus N]                                                      (one context + host thread per GPU, one process)
+//               [--dump-camera]                                                 (print the 16 doubles handed to update())
 //               [--option name=value ...]                                       (any rt_b200_set_option, e.g. accel=1)
 //               [--dump-scene]                                                  (print the parsed scene; needs no GPU)
 //
@@ -32,7 +34,7 @@ void usage(const char *argv0)
     std::fprintf(stderr,
                  "Usage: %s <scene.yml> [--width W] [--height H] [--max-reflections N] [--frames K]\n"
                  "          [--position x,y,z] [--yaw deg] [--pitch deg] [--orbit] [--out f.ppm] [--raw f.rgba]\n"
-                 "          [--kernel 0|1|2] [--option name=value ...] [--dump-scene]\n", argv0);
+                 "          [--kernel 0|1] [--gpus N] [--option name=value ...] [--dump-scene] [--dump-camera]\n", argv0);
 }
 
 void dump_scene(const rt_host::Scene &s)
@@ -86,7 +88,8 @@ int main(int argc, char **argv)
     }
     const char *scene_path = argv[1];
     long width = 0, height = 0, max_refl = -1, frames = 1, kernel = -1;
-    bool orbit = false, dump = false;
+    bool orbit = false, dump = false, dump_camera = false;
+    long gpus = 1;
     const char *out_ppm = nullptr, *out_raw = nullptr;
     std::vector<std::pair<std::string, long long>> options;
     rt_host::Camera cam;
@@ -116,6 +119,8 @@ int main(int argc, char **argv)
         else if (a == "--out") out_ppm = next();
         else if (a == "--raw") out_raw = next();
         else if (a == "--dump-scene") dump = true;
+        else if (a == "--dump-camera") dump_camera = true;
+        else if (a == "--gpus") gpus = std::atol(next());
         else if (a == "--option") {
             const std::string kv = next();
             const size_t eq = kv.find('=');
@@ -144,6 +149,11 @@ int main(int argc, char **argv)
             std::fprintf(stderr, "Empty frame or no frames requested\n");
             return EXIT_FAILURE;
         }
+        if (gpus < 1 || gpus > 64) {
+            std::fprintf(stderr, "--gpus must be 1..64\n");
+            return EXIT_FAILURE;
+        }
+        update_set_option("gpus", gpus);
         if (kernel >= 0) update_set_option("kernel", kernel);
         for (const auto &o : options) update_set_option(o.first.c_str(), o.second);
         init_update(0, scene);   // ray-tracer.cpp:215
@@ -155,6 +165,11 @@ int main(int argc, char **argv)
         for (long k = 0; k < frames; k++) {   // ray-tracer.cpp:222-243
             if (orbit && frames > 1) cam.yaw = 60.0 + 60.0 * (double) k / (double) (frames - 1);
             cam.matrix(m);
+            if (dump_camera) {   // what update() receives: glm::dmat4 in column-major order (ray-tracer.cpp:54-58,226)
+                std::printf("camera");
+                for (int q = 0; q < 16; q++) std::printf(" %.17g", m[q]);
+                std::printf("\n");
+            }
             ms = update(m);
             n_since++;
             const auto now = std::chrono::steady_clock::now();

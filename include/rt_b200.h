@@ -56,7 +56,7 @@ typedef struct {
     uint64_t tests_cubic;
     uint64_t fp64_confirms;   /* sphere tests that fell through the FP32 filter to the exact FP64 test */
     uint64_t cubic_exact;     /* cubic-class tests that needed the exact FP64 expansion + solve (the others were
-                               * decided by the FP32 filter); kernel 1 only, kernels 0 and 2 test exactly and leave 0 */
+                               * decided by the FP32 filter); kernel 1 only, kernel 0 tests exactly and leaves 0 */
 } rt_b200_counters;
 
 /* == init_update(texture, scene), update.h:6.
@@ -127,20 +127,33 @@ const char *rt_b200_last_error(void);
 int rt_b200_comm_unique_id(void *id_out /* RT_B200_UNIQUE_ID_BYTES */);
 int rt_b200_comm_init(rt_b200_ctx *ctx, const void *id /* RT_B200_UNIQUE_ID_BYTES */);
 
-/* Fused gather (optional, after rt_b200_comm_init): instead of all-gathering packed strips, every rank's render
- * kernel stores its pixels straight into ONE assembled frame that lives on rank 0 (double-buffered), through a CUDA
- * IPC mapping over NVLink; a 4-byte all-reduce is the frame-complete barrier.  Rank 0 exports, the host hands the
- * 64 bytes to every rank, and every rank (rank 0 included) attaches.  Afterwards rt_b200_gather returns rank 0's
- * frame on every rank (a peer-memory pointer on ranks > 0). */
+/* Fused gather (optional): instead of all-gathering packed strips, every rank's render kernel stores its pixels straight
+ * into ONE assembled frame that lives on rank 0 (two of them, used alternately) — a CUDA IPC mapping over NVLink for
+ * one process per GPU, plain peer access for contexts of one process — so the transfer overlaps the tracing tile by
+ * tile.  Rank 0 exports, the host hands the 64 bytes to every rank, and every rank (rank 0 included) attaches after
+ * rt_b200_comm_init; contexts of ONE process attach with rt_b200_frame_attach_peer instead (no IPC handle, no NCCL).
+ * Frame-complete is signalled through sequence words behind the frames in rank 0's memory (option "flag_barrier" 1, the
+ * default): every rank publishes flags[rank] = frame number after a system-scope fence, and RANK 0 — the consumer —
+ * waits for all of them inside its own rt_b200_update.  Guarantees:
+ *   - when rank 0's rt_b200_update returns, the frame is complete; rt_b200_gather on rank 0 hands it out;
+ *   - a rank > 0 returns when its OWN pixels are stored; rt_b200_gather there returns a peer pointer to rank 0's
+ *     frame, which other ranks may still be writing — a host that wants to read it on rank r > 0 adds its own
+ *     barrier after rank 0 has returned (tools/multi_gpu_check.py does);
+ *   - no rank overwrites a frame rank 0 may still be reading: rank r starts frame k only after rank 0 has entered
+ *     frame k - 1 (two buffers).
+ * With "flag_barrier" 0 a 4-byte NCCL all-reduce is the barrier instead (every rank waits for every rank; needs the
+ * communicator).  All ranks must call rt_b200_update for every frame, each from its own host thread or process: rank
+ * 0's call does not return before the others have rendered. */
 int rt_b200_frame_export(rt_b200_ctx *ctx, void *handle_out /* RT_B200_IPC_HANDLE_BYTES */);
 int rt_b200_frame_attach(rt_b200_ctx *ctx, const void *handle /* RT_B200_IPC_HANDLE_BYTES */);
+/* Same-process form: `owner` is rank 0's context (after rt_b200_frame_export) living in THIS process, possibly on
+ * another device; rank 0 passes its own context.  New with the multi-GPU path (the reference is one GPU). */
+int rt_b200_frame_attach_peer(rt_b200_ctx *ctx, rt_b200_ctx *owner);
 
 /* ---- introspection and tuning -------------------------------------------------------------------- */
 int rt_b200_get_counters(rt_b200_ctx *ctx, rt_b200_counters *out);
 
-/* Options: "kernel"     0 = exact FP64 kernel (thread per pixel), 1 = wavefront kernel (default),
- *                       2 = queue kernel (path records + per-family FP32 sphere tables; falls back to 1 when the
- *                           scene exceeds its parameter block)
+/* Options: "kernel"     0 = exact FP64 kernel (thread per pixel; the on-device cross-check), 1 = wavefront kernel (default)
  *          "host_bands" row bands of rt_b200_update_to_host (0 = automatic, about 4 MB each)
  *          "strip_rows" image rows per strip of the multi-GPU interleave (default 8)
  *          "count"      1 = maintain rt_b200_counters (default), 0 = skip them
@@ -168,7 +181,9 @@ int rt_b200_set_option(rt_b200_ctx *ctx, const char *name, int64_t value);
 /* Split timing of the last update, milliseconds: [0] render kernels, [1] gather (all-gather + unpack). */
 int rt_b200_get_timing(rt_b200_ctx *ctx, float out_ms[2]);
 
-/* Kernels launched by the last rt_b200_update / rt_b200_update_to_host on this rank (render + table setup + unpack). */
+/* Kernels of THIS library launched by the last rt_b200_update / rt_b200_update_to_host on this rank: render launches
+ * (one per row band), the strip un-interleave after an NCCL all-gather, and — kernel 0 with the fused gather only — the
+ * sequence-word kernels (kernel 1 does that hand-shake inside the render kernel). */
 int rt_b200_get_launches(rt_b200_ctx *ctx, uint32_t *launches);
 
 /* Structural class counts of the uploaded scene: planes, spheres, quadrics, cubics. */

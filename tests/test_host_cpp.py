@@ -191,6 +191,48 @@ def test_headless_driver_frame_equals_python_host(pkg, exe, scenes_dir, tmp_path
         assert np.array_equal(px, got[::-1, :, :3])
 
 
+def _run_driver(exe, scenes_dir, name, tmp_path, tag, w, h, pos, yaw, pitch, extra=()):
+    raw = tmp_path / "{}_{}.rgba".format(name, tag)
+    out = subprocess.run([exe, os.path.join(scenes_dir, name + ".yml"), "--width", str(w), "--height", str(h),
+                          "--max-reflections", "4", "--frames", "2", "--position", "{},{},{}".format(*pos),
+                          "--yaw", str(yaw), "--pitch", str(pitch), "--raw", str(raw), "--dump-camera"] + list(extra),
+                         capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr
+    cams = [ln.split()[1:] for ln in out.stdout.splitlines() if ln.startswith("camera ")]
+    assert len(cams) == 2 and len(cams[-1]) == 16, out.stdout
+    m = np.array([float(v) for v in cams[-1]], dtype=np.float64)
+    return np.fromfile(raw, dtype=np.uint8).reshape(h, w, 4), m
+
+
+@pytest.mark.gpu
+def test_headless_driver_against_the_oracle(pkg, oracle, exe, scenes_dir, tmp_path):
+    """the C++ driver's frame (ray-tracer.cpp:44-58,215-245 without the window) checked against the
+    CPU oracle fed with the very 16 doubles the driver handed to update() (--dump-camera) — +-1 LSB, <= 0.1 % beyond —
+    on one GPU and with --gpus 2 / 3 (one process, one context and host thread per GPU, fused gather over peer access).
+    On a box with a single GPU the ranks share device 0 (option same_device): same code path, same hand-shake."""
+    import torch
+    from parity import assert_parity
+    n_dev = torch.cuda.device_count()
+    w, h = 480, 270
+    for name, pos, yaw, pitch in (("dingdong", (0.0, 0.0, 0.0), 90.0, 0.0), ("reflection_test", (3.0, 2.0, -5.0), 80.0, -10.0),
+                                  ("20spheres", (1.0, 0.5, -2.0), 95.0, 5.0)):
+        sc = pkg.load_from_file(os.path.join(scenes_dir, name + ".yml")).with_overrides(width=w, height=h, max_reflections=4)
+        one, m = _run_driver(exe, scenes_dir, name, tmp_path, "g1", w, h, pos, yaw, pitch)
+        want = oracle.quantize_rgba8(oracle.PortOracle(sc).render(m, threads=os.cpu_count()))
+        res = assert_parity(one, want, name + " C++ driver, 1 GPU")
+        assert res["exact_frac"] > 0.999, res
+        if oracle.have_ref():
+            rgb, _ = oracle.RefCpu(sc).render_rows(m, 100, 140, 1, threads=1)
+            assert_parity(one[100:140], oracle.quantize_rgba8(rgb), name + " C++ driver rows 100..139 (reference build)")
+        for gpus in (2, 3):
+            extra = ["--gpus", str(gpus), "--option", "strip_rows=8"]
+            if n_dev < gpus:
+                extra += ["--option", "same_device=1"]
+            many, m2 = _run_driver(exe, scenes_dir, name, tmp_path, "g{}".format(gpus), w, h, pos, yaw, pitch, extra)
+            assert np.array_equal(m2, m)
+            assert np.array_equal(many, one), "{}: --gpus {} frame differs from the 1-GPU frame".format(name, gpus)
+
+
 def test_headless_driver_rejects_malformed_option(exe, scenes_dir):
     """--option wants name=value; anything else prints the usage text (needs no GPU)."""
     for bad in ("accel", "=1"):

@@ -306,6 +306,56 @@ def test_shared_host_frame_ranks_as_processes(pkg, rt, scenes_dir, tmp_path, wor
         rt.host_free_shared(ptr)
 
 
+def test_contexts_on_several_devices_in_one_process(pkg, rt, scenes_dir):
+    """One process, one context per device (rt_b200.h allows a thread per GPU): the >48 KB dynamic shared memory
+    attribute of the render kernels is per DEVICE, so the second device must get it too; and the same-process fused
+    gather (rt_b200_frame_attach_peer): every rank's kernel stores into rank 0's frame, rank 0's update returns when the
+    frame is whole.  With fewer GPUs than ranks the ranks share device 0 — same kernels, same hand-shake."""
+    import threading
+    import torch
+    from cuda_ray_tracer_b200 import camera
+    n_dev = torch.cuda.device_count()
+    m = camera.TEST_POSES["pose_a"]
+    for name in ("dingdong", "20spheres"):
+        sc = _load(pkg, scenes_dir, name, width=777, height=431, max_reflections=4)
+        with rt.Renderer(sc, device=0) as r:
+            r.update(m)
+            want = r.gather()
+        if n_dev >= 2:      # independent whole frames on two devices from one process
+            with rt.Renderer(sc, device=0) as a, rt.Renderer(sc, device=1) as b:
+                a.update(m)
+                b.update(m)
+                assert np.array_equal(a.gather(), want) and np.array_equal(b.gather(), want)
+        for world in (2, 4):
+            rs = [rt.Renderer(sc, device=(k if k < n_dev else 0), rank=k, world_size=world) for k in range(world)]
+            try:
+                for r in rs:
+                    r.set_option("strip_rows", 8)
+                rs[0].frame_export()
+                for r in rs:
+                    r.frame_attach_peer(rs[0])
+                for frame in range(3):
+                    errs = []
+
+                    def run(r):
+                        try:
+                            r.update(m)
+                        except Exception as e:      # noqa: BLE001
+                            errs.append(e)
+                    ts = [threading.Thread(target=run, args=(r,)) for r in rs[1:]]
+                    for t in ts:
+                        t.start()
+                    rs[0].update(m)                 # returns when every rank's pixels are in rank 0's frame
+                    got = rs[0].gather()
+                    for t in ts:
+                        t.join()
+                    assert not errs, errs
+                    assert np.array_equal(got, want), (name, world, frame)
+            finally:
+                for r in reversed(rs):
+                    r.close()
+
+
 def test_cubic_filter_and_culling_paths(pkg, rt, oracle):
     """Kernel 1's FP32 cubic filter (cached halves / generic path / many lights) and the light culling: with every
     combination of the two options the frame equals the exact kernel's, and the oracle's."""
