@@ -234,8 +234,10 @@ def run_b200(args):
         r = binding.Renderer(sc, device=local, rank=rank, world_size=world)
         r.set_option("kernel", args.kernel)
         r.set_option("accel", args.accel)
+        r.set_option("variant", args.variant)
         if world > 1:
             r.set_option("strip_rows", args.strip_rows)
+            r.set_option("dynamic_tiles", args.dynamic)
             ident = [binding.comm_unique_id() if rank == 0 else None]
             dist.broadcast_object_list(ident, src=0)
             r.comm_init(ident[0])
@@ -386,7 +388,7 @@ def run_b200(args):
                                  "what": "0 = brute force over all objects like the reference (the roofline is quoted on this); 1 = sphere "
                                          "class through the uniform grid (SURVEY §8 f4): identical frames, canonical flops still those "
                                          "of the brute-force census, so roofline.frac is reference-equivalent work and can exceed 1"},
-                       "parallelism": "strips{}x{}rows,{}".format(world, args.strip_rows, "p2p-store+flags" if fused else
+                       "parallelism": "strips{}x{}rows,{}".format(world, args.strip_rows, ("p2p-store+flags,dynamic-groups" if args.dynamic else "p2p-store+flags,static-strips") if fused else
                                                                   "nccl-allgather") if world > 1 else "1gpu",
                        "timing": "CUDA events on the render stream per frame, summed; max over ranks",
                        "ms_per_step_wall": ms_wall, "frame_check": frame_check,
@@ -566,6 +568,9 @@ def main():
                     "copies its strips into one shared host frame, or rank 0 gathers on the device and copies alone")
     ap.add_argument("--accel", type=int, default=0, choices=[-1, 0, 1], help="sphere-class grid (separate mode, SURVEY §8 f4): "
                     "0 = brute force like the reference (default, what the roofline is quoted on), 1 = on, -1 = library default")
+    ap.add_argument("--dynamic", type=int, default=1, choices=[0, 1], help="multi-GPU, fused gather: 1 = row groups of the image are "
+                    "handed out to the GPUs on demand by a counter in rank 0's memory (SURVEY §8 f3), 0 = static 8-row strips")
+    ap.add_argument("--variant", type=int, default=0, help="wavefront kernel shape (0 = automatic)")
     ap.add_argument("--no-cull", dest="cull", action="store_false", help="trace every shadow ray the reference casts")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-frame-check", action="store_true", help="skip the untimed frame verification before the timed loops")

@@ -158,6 +158,8 @@ cudaError_t upload(const std::vector<T> &host, T **dev)
 } // namespace
 
 #define RT_MAX_BANDS 16
+#define RT_DYN_GROUP_ROWS 16   /* rows per group of the dynamic split: a multiple of every variant's tile height */
+#define RT_DYN_AHEAD 4         /* slots whose group is fetched in advance (and assigned statically at the start) */
 #define RT_GRID_AUTO_SPHERES 64
 
 struct rt_b200_ctx {
@@ -219,6 +221,12 @@ struct rt_b200_ctx {
     // sequence words behind the two frames in rank 0's allocation: flags[rank] = last frame this rank finished,
     // go = last frame rank 0 started (back-pressure: rank r starts frame k only when go >= k - 1)
     unsigned *d_flags = nullptr, *d_go = nullptr;
+    // dynamic ownership of row groups across GPUs (WaveDyn in rt_wave.cuh): fused gather + kernel 1
+    unsigned long long *d_tiles = nullptr;   // [2] behind go in rank 0's allocation: the job's group counters
+    int *d_slot_group = nullptr;     // this GPU's slot -> group table
+    int dyn_max_slots = 0, dyn_n_groups = 0;
+    int dynamic_tiles = 1;           // option: 1 = on (default), 0 = every rank renders its own strips
+    bool dynamic_now = false;        // ... in effect for the frame being issued
     unsigned *h_timed_out = nullptr, *d_timed_out = nullptr;   // page-locked, mapped: the wait kernel's timeout report
     unsigned seq = 0;
     int flag_barrier = 1;            // 1: flag words (default), 0: 4-byte NCCL all-reduce
@@ -541,12 +549,20 @@ int launch_kernel(rt_b200_ctx *c, const rt::FrameParams &f, cudaStream_t stream,
         rt::WaveLaunch wl{c->d_tile_counter + 2 * counter_pair, c->d_cubic_mask, c->sphere_r2_max, c->shadow_cache, c->wave_variant, c->cubic_filter,
                           (c->cull_backfacing && c->cull_safe) ? 1 : 0,
                           (c->accel > 0 || (c->accel < 0 && c->view.n_sphere >= RT_GRID_AUTO_SPHERES)) ? 1 : 0,
-                          nullptr, nullptr, nullptr, 0u};
+                          nullptr, nullptr, nullptr, 0u, c->rank, c->world, nullptr, nullptr, 0, 0, 0, 0};
         if (c->sync_in_kernel) {   // fused gather: the render kernel does the frame hand-shake itself
             wl.sync_go = c->d_go;
             wl.sync_flags = c->d_flags;
             wl.sync_timed_out = c->d_timed_out;
             wl.sync_seq = c->seq;
+            if (c->dynamic_now) {
+                wl.dyn_counters = c->d_tiles;
+                wl.dyn_slot_group = c->d_slot_group;
+                wl.dyn_n_groups = c->dyn_n_groups;
+                wl.dyn_group_rows = RT_DYN_GROUP_ROWS;
+                wl.dyn_max_slots = c->dyn_max_slots;
+                wl.dyn_ahead = RT_DYN_AHEAD;
+            }
         }
         const cudaError_t e = rt::launch_render_wave(c->view, f, wl, stream);
         if (e != cudaSuccess) {
@@ -660,6 +676,24 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
     CUDA_TRY(cudaEventRecord(c->ev_start, c->stream));
     // kernel 1 does the go / flag hand-shake of the fused gather in its own prologue / epilogue: no extra launches
     c->sync_in_kernel = shared && c->flag_barrier && c->kernel_kind == 1;
+    // Dynamic tile ownership: the frame is one tile space for all GPUs; this rank's launch describes
+    // the WHOLE image (as a single-rank frame) and its CTAs pull tiles from the job's counter in rank 0's memory.
+    c->dynamic_now = c->sync_in_kernel && c->dynamic_tiles && c->d_tiles != nullptr;
+    if (c->dynamic_now) {
+        if (!c->d_slot_group) {
+            c->dyn_n_groups = (c->height + RT_DYN_GROUP_ROWS - 1) / RT_DYN_GROUP_ROWS;
+            c->dyn_max_slots = c->dyn_n_groups + RT_DYN_AHEAD + 1;
+            CUDA_TRY(cudaMalloc((void **) &c->d_slot_group, sizeof(int) * (size_t) c->dyn_max_slots));
+            CUDA_TRY(rt::launch_dyn_table_init(c->d_slot_group, c->dyn_max_slots, RT_DYN_AHEAD, c->dyn_n_groups, c->rank, c->world, c->stream));
+        }
+        f.strip_rows = c->height;
+        f.rank = 0;
+        f.world = 1;
+        f.local_rows = c->height;
+        band_start[0] = 0;
+        band_start[1] = c->dyn_n_groups * RT_DYN_GROUP_ROWS;   // whole groups (rows past the image are masked by local_rows);
+                                                               // n_bands == 1: the fused gather never streams
+    }
     if (shared && c->flag_barrier) {
         c->seq++;
         if (!c->sync_in_kernel) {
@@ -948,6 +982,7 @@ int rt_b200_frame_attach(rt_b200_ctx *c, const void *handle)
     if (c->world > 1000) return fail(RT_B200_ERR_ARG, "too many ranks for the sync words");
     c->d_flags = reinterpret_cast<unsigned *>(c->d_shared_base + 2 * px);   // [world] + go
     c->d_go = c->d_flags + 1000;
+    c->d_tiles = reinterpret_cast<unsigned long long *>(c->d_flags + 1008);
     c->seq = 0;
     c->shared_ready = true;
     CUDA_TRY(cudaMemset(c->d_barrier, 0, sizeof(int)));
@@ -986,6 +1021,7 @@ int rt_b200_frame_attach_peer(rt_b200_ctx *c, rt_b200_ctx *owner)
     c->d_shared[1] = c->d_shared_base + px;
     c->d_flags = reinterpret_cast<unsigned *>(c->d_shared_base + 2 * px);
     c->d_go = c->d_flags + 1000;
+    c->d_tiles = reinterpret_cast<unsigned long long *>(c->d_flags + 1008);
     c->seq = 0;
     c->shared_ready = true;
     return RT_B200_OK;
@@ -1046,6 +1082,7 @@ int rt_b200_destroy(rt_b200_ctx *c)
     cudaFree(c->d_cubic_mask);
     cudaFree(c->d_grid_cells);
     cudaFree(c->d_grid_items);
+    cudaFree(c->d_slot_group);
     if (c->ev_start) cudaEventDestroy(c->ev_start);
     if (c->ev_render) cudaEventDestroy(c->ev_render);
     if (c->ev_end) cudaEventDestroy(c->ev_end);
@@ -1124,6 +1161,9 @@ int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
     }
     else if (!std::strcmp(name, "flag_barrier")) {
         c->flag_barrier = value != 0;
+    }
+    else if (!std::strcmp(name, "dynamic_tiles")) {
+        c->dynamic_tiles = value ? 1 : 0;
     }
     else if (!std::strcmp(name, "cull_backfacing")) {
         c->cull_backfacing = value ? 1 : 0;

@@ -137,6 +137,24 @@ __global__ void sync_wait_kernel(const unsigned *words, int first, int n, unsign
     }
 }
 
+__global__ void dyn_table_init_kernel(int *slot_group, int max_slots, int ahead, int n_groups, int rank, int world)
+{
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < max_slots; k += gridDim.x * blockDim.x) {
+        int g = -1;
+        if (k < ahead) {
+            g = k * world + rank;
+            if (g >= n_groups) g = -2;
+        }
+        slot_group[k] = g;
+    }
+}
+
+cudaError_t launch_dyn_table_init(int *slot_group, int max_slots, int ahead, int n_groups, int rank, int world, cudaStream_t stream)
+{
+    dyn_table_init_kernel<<<(max_slots + 255) / 256, 256, 0, stream>>>(slot_group, max_slots, ahead, n_groups, rank, world);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_sync_store(unsigned *word, unsigned value, cudaStream_t stream)
 {
     sync_store_kernel<<<1, 1, 0, stream>>>(word, value);

@@ -22,7 +22,14 @@ struct WaveLaunch {
     // fused multi-GPU gather: sequence words in rank 0's memory (go == nullptr: none), see WaveSync in rt_wave.cuh
     unsigned *sync_go, *sync_flags, *sync_timed_out;
     unsigned sync_seq;
+    int sync_rank, sync_world;          // this GPU's rank in the job (FrameParams may describe the whole image as one rank's)
+    // dynamic ownership of row groups across GPUs (WaveDyn in rt_wave.cuh); dyn_counters == nullptr: static strips
+    unsigned long long *dyn_counters;   // [2] in rank 0's memory
+    int *dyn_slot_group;                // this GPU's slot -> group table
+    int dyn_n_groups, dyn_group_rows, dyn_max_slots, dyn_ahead;
 };
+// (re)initialise a slot -> group table: the first `ahead` slots statically, the rest "not fetched yet"
+cudaError_t launch_dyn_table_init(int *slot_group, int max_slots, int ahead, int n_groups, int rank, int world, cudaStream_t stream);
 cudaError_t launch_render_wave(const SceneView &scene, const FrameParams &frame, const WaveLaunch &wl, cudaStream_t stream);
 
 // Undo the strip interleave after the all-gather: gathered = [world][local_rows][width] -> frame[height][width].

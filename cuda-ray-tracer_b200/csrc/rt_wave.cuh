@@ -66,6 +66,8 @@ struct WaveCtl {
     int occ_found[2];            // occluders found so far by [0] the sphere pass, [1] the cubic pass
     int prim_rays, prim_hits;    // recent primary rays / hits of this CTA (decayed): the cubic filter runs on primary
     int prim_filter;             // rays only while enough of them miss for a proven miss to pay for the filter
+    unsigned chunk_next, chunk_end;   // tiles already pulled from the counter and not rendered yet (thread 0 only)
+    int dyn_slot, dyn_group;     // dynamic ownership: the last slot -> group lookup (thread 0 only)
     double cam_x[32], cam_y[MAX_WARPS];   // camera-plane coordinates of the current tile's 32 columns / W/32 rows
 };
 
@@ -74,12 +76,31 @@ struct WaveCtl {
 //             frame (rank 0 may still be reading the frame that used this buffer two frames ago)
 //   epilogue  the last CTA to finish publishes flags[rank] = seq after a system-scope fence; on rank 0 it then
 //             waits until every rank's flag has reached seq, so the kernel's completion means "frame assembled"
+//   dyn        dynamic ownership of row groups across GPUs, see WaveDyn below
 struct WaveSync {
     unsigned *go;                // in rank 0's memory (null: no fused gather, nothing of this runs)
     unsigned *flags;             // [world], in rank 0's memory
     unsigned *timed_out;         // mapped host word
     unsigned seq;
     int rank, world;
+};
+
+// Dynamic ownership of the image across GPUs (fused gather only: any GPU may store any pixel into rank 0's frame).
+// The image is cut into GROUPS of group_rows rows.  A job-wide counter in rank 0's memory hands out groups; each GPU
+// keeps a table slot -> group and its CTAs pull TILES from the GPU's own counter as before: local tile t is tile
+// t % tiles_per_group of slot t / tiles_per_group.  The CTA that takes the first tile of slot k fetches the group of
+// slot k + ahead from the job's counter (one system-scope atomic over NVLink, ~3 us, for a whole group of tiles) and
+// publishes it in the table, so by the time anybody needs slot k + ahead its group is known; the first `ahead` slots
+// of every GPU are assigned statically (group = slot * world + rank).  Remote traffic: one atomic per group.  A GPU that
+// is done early simply takes more groups — no GPU waits for another while there is work left.
+//   counters[2]  in rank 0's memory, used alternately: frame seq counts in counters[seq & 1]; rank 0 zeroes the other
+//                before it publishes go = seq (nobody counts there: rank 0 finished frame seq - 1 only after every
+//                rank had, and nobody starts frame seq + 1 before go >= seq)
+//   slot_group   this GPU's table; -1 = not fetched yet, -2 = no groups left; re-armed by the last CTA of each launch
+struct WaveDyn {
+    unsigned long long *counters;   // null: static strips (each rank renders its own strips)
+    int *slot_group;
+    int n_groups, group_rows, max_slots, ahead;
 };
 
 struct WaveConfig {
@@ -91,6 +112,7 @@ struct WaveConfig {
     int cull_backfacing;         // skip shadow rays of lights whose Lambert factor is 0 at the hit (they add exactly 0)
     unsigned long long *tile_counter;   // [0] next tile, [1] CTAs finished; the last CTA leaves both at 0
     WaveSync sync;
+    WaveDyn dyn;
     const unsigned *cubic_mask;  // global copy
     float sphere_r2_max;
 };

@@ -22,6 +22,59 @@ __device__ __forceinline__ void store_primary(uchar4 *out, size_t index, bool fi
     }
 }
 
+// Next tile for this CTA (thread 0 only): index into the tile space of the launch's frame, n_tiles = none left.
+// Static split: this GPU's counter counts the tiles of its own strips.  Dynamic ownership (WaveDyn): the counter
+// counts tiles of SLOTS; the slot's row group comes from the table, which is filled `ahead` slots in advance from the
+// job's counter in rank 0's memory.
+// The counter's round trip (~0.5 us to L2 and back, with the whole CTA waiting at the barrier behind it) is paid once
+// per CHUNK of tiles: up to four while plenty of tiles are left, one near the end of the frame (guided self-scheduling:
+// remaining / (8 x CTAs)), so the tail of the frame is as fine-grained as before.
+__device__ __forceinline__ int next_tile_index(const WaveConfig &cfg, WaveCtl &ctl, int n_tiles, int tile_rows)
+{
+    if (ctl.chunk_next == ctl.chunk_end) {
+        // tiles this GPU still expects to hand out: of its own strips (static) or of an equal share of the image (dynamic)
+        const unsigned pulled = ctl.chunk_end;   // a lower bound of the counter
+        const unsigned share = cfg.dyn.counters != nullptr ? (unsigned) n_tiles / (unsigned) cfg.sync.world : (unsigned) n_tiles;
+        const unsigned left = share > pulled ? share - pulled : 0u;
+        unsigned want = left / (8u * gridDim.x);
+        want = want < 1u ? 1u : (want > 4u ? 4u : want);
+        const unsigned t = atomicAdd(reinterpret_cast<unsigned *>(cfg.tile_counter), want);
+        ctl.chunk_next = t;
+        ctl.chunk_end = t + want;
+    }
+    const unsigned t = ctl.chunk_next++;
+    if (cfg.dyn.counters == nullptr) return t < (unsigned) n_tiles ? (int) t : n_tiles;
+    const unsigned tiles_per_group = (unsigned) (cfg.tiles_x * (cfg.dyn.group_rows / tile_rows));
+    const unsigned k = t / tiles_per_group, r = t - k * tiles_per_group;
+    if (k >= (unsigned) cfg.dyn.max_slots) return n_tiles;      // cannot happen before the end marker has been seen
+    if (r == 0u && k + cfg.dyn.ahead < (unsigned) cfg.dyn.max_slots) {
+        // first tile of slot k: fetch the group of slot k + ahead (groups 0 .. world * ahead - 1 were assigned statically)
+        const unsigned got = atomicAdd_system(reinterpret_cast<unsigned *>(cfg.dyn.counters + (cfg.sync.seq & 1u)), 1u);
+        const long long grp = (long long) got + (long long) cfg.sync.world * cfg.dyn.ahead;
+        const int val = grp < cfg.dyn.n_groups ? (int) grp : -2;
+        asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(cfg.dyn.slot_group + k + cfg.dyn.ahead), "r"(val) : "memory");
+    }
+    int grp = ctl.dyn_group;
+    if (ctl.dyn_slot != (int) k) {      // one table look-up per slot and CTA, not per tile
+        const long long t0 = clock64();
+        for (;;) {
+            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(grp) : "l"(cfg.dyn.slot_group + k) : "memory");
+            if (grp != -1) break;
+            if (clock64() - t0 > 40000000000LL) {   // ~20 s: report instead of hanging the box
+                *cfg.sync.timed_out = 1u;
+                grp = -2;
+                break;
+            }
+            __nanosleep(40);
+        }
+        ctl.dyn_slot = (int) k;
+        ctl.dyn_group = grp;
+    }
+    if (grp < 0) return n_tiles;
+    const unsigned tile_row = (unsigned) grp * (unsigned) (cfg.dyn.group_rows / tile_rows) + r / (unsigned) cfg.tiles_x;
+    return (int) (tile_row * (unsigned) cfg.tiles_x + r % (unsigned) cfg.tiles_x);
+}
+
 __device__ __forceinline__ float blend(float out, float ratio, float c) { return (1.0f - ratio) * out + ratio * c; }
 
 } // namespace
@@ -83,6 +136,9 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
             ctl.occ_found[0] = ctl.occ_found[1] = 0;
             ctl.prim_rays = ctl.prim_hits = 0;
             ctl.prim_filter = 1;
+            ctl.chunk_next = ctl.chunk_end = 0u;
+            ctl.dyn_slot = -1;
+            ctl.dyn_group = -1;
         }
         if (tid < LIGHT_CHUNK) ctl.shadow_cache[tid] = -1;
         __syncthreads();
@@ -108,14 +164,22 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         // fused gather: frame hand-shake with rank 0 (WaveSync) — before the first pixel leaves this GPU
         if (cfg.sync.go != nullptr && tid == 0) {
             if (cfg.sync.rank == 0) {
-                if (blockIdx.x == 0) asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(cfg.sync.go), "r"(cfg.sync.seq) : "memory");
+                if (blockIdx.x == 0) {
+                    if (cfg.dyn.counters != nullptr) cfg.dyn.counters[(cfg.sync.seq + 1u) & 1u] = 0ULL;   // the next frame's group counter (WaveDyn)
+                    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(cfg.sync.go), "r"(cfg.sync.seq) : "memory");
+                }
             }
             else {
+                // a rank may run one frame ahead of rank 0 (two frame buffers).  With dynamic ownership a rank that starts
+                // a frame early simply takes groups until the others join: work-conserving, nobody waits.  (Making
+                // everybody wait for rank 0 here would deadlock ranks that share one GPU: the waiting CTAs would hold
+                // the SM slots rank 0's kernel needs.)
+                const unsigned need = cfg.sync.seq - 1u;
                 const long long t0 = clock64();
                 for (;;) {
                     unsigned v;
                     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(cfg.sync.go) : "memory");
-                    if ((int) (v - (cfg.sync.seq - 1u)) >= 0) break;
+                    if ((int) (v - need) >= 0) break;
                     if (clock64() - t0 > 40000000000LL) {   // ~20 s: report instead of hanging the box
                         *cfg.sync.timed_out = 1u;
                         break;
@@ -134,7 +198,6 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
     const bool vec_ok = (f.width & 3) == 0;   // rows start 16-byte aligned (packed and assembled layout alike)
     bool tiles_left = true;
     unsigned waves = 0;
-
     for (;;) {
         if (COUNT && (++waves & 63u) == 0) {   // keep the 32-bit per-thread tallies far from overflow
             flush_tally(tl, f.counters);
@@ -143,7 +206,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         // ---- choose the next wave: pooled bounce rays when a full wave is waiting (or nothing else is left) ----
         if (tid == 0) {
             ctl.tile = -1;
-            if (ctl.pool_count < WAVE && tiles_left) ctl.tile = (int) atomicAdd(cfg.tile_counter, 1ULL);
+            if (ctl.pool_count < WAVE && tiles_left) ctl.tile = next_tile_index(cfg, ctl, n_tiles, TILE_ROWS);
             ctl.n_hits = 0;
         }
         __syncthreads();
@@ -400,6 +463,20 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         }
         ctl.tile = last ? 1 : 0;
     }
+    if (cfg.dyn.counters != nullptr) {
+        // the last CTA re-arms this GPU's slot table for the next launch (every other CTA is done with it)
+        __syncthreads();
+        if (ctl.tile) {
+            for (int k = tid; k < cfg.dyn.max_slots; k += WAVE) {
+                int grp = -1;
+                if (k < cfg.dyn.ahead) {
+                    grp = k * cfg.sync.world + cfg.sync.rank;
+                    if (grp >= cfg.dyn.n_groups) grp = -2;
+                }
+                cfg.dyn.slot_group[k] = grp;
+            }
+        }
+    }
     if (cfg.sync.go != nullptr && cfg.sync.rank == 0) {
         __syncthreads();
         if (ctl.tile && tid < cfg.sync.world) {   // rank 0 consumes the frame: wait for every rank's flag
@@ -492,7 +569,8 @@ cudaError_t launch_render_wave_t(const SceneView &scene, const FrameParams &fram
     WaveConfig cfg;
     cfg.tiles_x = cfg.tiles_y = 0;
     cfg.tile_counter = wl.tile_counter;
-    cfg.sync = WaveSync{wl.sync_go, wl.sync_flags, wl.sync_timed_out, wl.sync_seq, frame.rank, frame.world};
+    cfg.sync = WaveSync{wl.sync_go, wl.sync_flags, wl.sync_timed_out, wl.sync_seq, wl.sync_rank, wl.sync_world};
+    cfg.dyn = WaveDyn{wl.dyn_counters, wl.dyn_slot_group, wl.dyn_n_groups, wl.dyn_group_rows, wl.dyn_max_slots, wl.dyn_ahead};
     cfg.cubic_mask = wl.cubic_mask;
     cfg.sphere_r2_max = wl.sphere_r2_max;
     cfg.use_shadow_cache = wl.shadow_cache >= 0 ? wl.shadow_cache : (scene.n_objects >= 8 ? 1 : 0);

@@ -326,11 +326,12 @@ def test_contexts_on_several_devices_in_one_process(pkg, rt, scenes_dir):
                 a.update(m)
                 b.update(m)
                 assert np.array_equal(a.gather(), want) and np.array_equal(b.gather(), want)
-        for world in (2, 4):
+        for world, dynamic in ((2, 1), (4, 1), (3, 0)):
             rs = [rt.Renderer(sc, device=(k if k < n_dev else 0), rank=k, world_size=world) for k in range(world)]
             try:
                 for r in rs:
                     r.set_option("strip_rows", 8)
+                    r.set_option("dynamic_tiles", dynamic)   # 1: tiles of the whole image from rank 0's counter; 0: own strips
                 rs[0].frame_export()
                 for r in rs:
                     r.frame_attach_peer(rs[0])
@@ -350,7 +351,7 @@ def test_contexts_on_several_devices_in_one_process(pkg, rt, scenes_dir):
                     for t in ts:
                         t.join()
                     assert not errs, errs
-                    assert np.array_equal(got, want), (name, world, frame)
+                    assert np.array_equal(got, want), (name, world, dynamic, frame)
             finally:
                 for r in reversed(rs):
                     r.close()

@@ -24,14 +24,15 @@ for name, sc, strip in cases:
     ms1 = min(single.update(m) for _ in range(3))
     ref = single.gather()
     single.close()
-    for mode in ("nccl", "p2p-allreduce", "p2p"):
+    for mode in ("nccl", "p2p-allreduce", "p2p-static", "p2p"):
         r = binding.Renderer(sc, device=local, rank=rank, world_size=world)
         r.set_option("strip_rows", strip)
         ident = [binding.comm_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ident, src=0)
         r.comm_init(ident[0])
         if mode != "nccl":
-            r.set_option("flag_barrier", 1 if mode == "p2p" else 0)
+            r.set_option("flag_barrier", 0 if mode == "p2p-allreduce" else 1)
+            r.set_option("dynamic_tiles", 1 if mode == "p2p" else 0)   # p2p: row groups handed out by rank 0's counter (f3)
             handle = [r.frame_export() if rank == 0 else None]
             dist.broadcast_object_list(handle, src=0)
             r.frame_attach(handle[0])
@@ -39,15 +40,20 @@ for name, sc, strip in cases:
         for i in range(4):      # several frames: the shared frame is double-buffered
             ms = r.update(camera.TEST_POSES["pose_b" if i % 2 else "pose_a"])
         ms = r.update(m)
-        if mode == "p2p":
+        if mode in ("p2p", "p2p-static"):
             dist.barrier()      # flag words: only rank 0 waits for every rank; the others need a host barrier to read
         multi = r.gather()
         dist.barrier()          # nobody starts the next frame while a peer still reads this one
         t = r.timing()
         same = bool(np.array_equal(multi, ref))
         ok &= same
-        print("rank {} {} world {} strips {} {}: identical={} multi {:.3f} ms (render {:.3f} gather {:.3f}) single {:.3f} ms".format(
-            rank, name, world, strip, mode, same, ms, t["render_ms"], t["gather_ms"], ms1), flush=True)
+        r.set_option("count", 1)
+        r.update(m)
+        px = r.counters()["primary_rays"]      # pixels THIS rank rendered: the dynamic split moves work between ranks
+        r.set_option("count", 0)
+        dist.barrier()
+        print("rank {} {} world {} strips {} {}: identical={} multi {:.3f} ms (render {:.3f} gather {:.3f}) single {:.3f} ms, pixels here {}".format(
+            rank, name, world, strip, mode, same, ms, t["render_ms"], t["gather_ms"], ms1, px), flush=True)
         r.close()
         dist.barrier()
     # host frame shared by all ranks: every rank's copy engine writes its own strips (no NVLink, no communicator)
