@@ -158,8 +158,9 @@ cudaError_t upload(const std::vector<T> &host, T **dev)
 } // namespace
 
 #define RT_MAX_BANDS 16
-#define RT_DYN_GROUP_ROWS 16   /* rows per group of the dynamic split: a multiple of every variant's tile height */
-#define RT_DYN_AHEAD 4         /* slots whose group is fetched in advance (and assigned statically at the start) */
+#define RT_DYN_AHEAD 2         /* slots whose group is fetched in advance (and assigned statically at the start): a group of
+                                  8 x 3840 pixels is ~2 us of one GPU's work, the fetch ~3 us; what a GPU has reserved when
+                                  the groups run out is the tail imbalance (ahead 4 x 16 rows cost 17 us per frame) */
 #define RT_GRID_AUTO_SPHERES 64
 
 struct rt_b200_ctx {
@@ -224,7 +225,7 @@ struct rt_b200_ctx {
     // dynamic ownership of row groups across GPUs (WaveDyn in rt_wave.cuh): fused gather + kernel 1
     unsigned long long *d_tiles = nullptr;   // [2] behind go in rank 0's allocation: the job's group counters
     int *d_slot_group = nullptr;     // this GPU's slot -> group table
-    int dyn_max_slots = 0, dyn_n_groups = 0;
+    int dyn_max_slots = 0, dyn_n_groups = 0, dyn_group_rows = 0;
     int dynamic_tiles = 1;           // option: 1 = on (default), 0 = every rank renders its own strips
     bool dynamic_now = false;        // ... in effect for the frame being issued
     unsigned *h_timed_out = nullptr, *d_timed_out = nullptr;   // page-locked, mapped: the wait kernel's timeout report
@@ -533,6 +534,15 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
 
 namespace {
 
+// What the wavefront kernel's launcher needs from the context (the frame hand-shake words are added per frame).
+rt::WaveLaunch wave_launch_of(const rt_b200_ctx *c, int counter_pair)
+{
+    return rt::WaveLaunch{c->d_tile_counter + 2 * counter_pair, c->d_cubic_mask, c->sphere_r2_max, c->shadow_cache, c->wave_variant,
+                          c->cubic_filter, (c->cull_backfacing && c->cull_safe) ? 1 : 0,
+                          (c->accel > 0 || (c->accel < 0 && c->view.n_sphere >= RT_GRID_AUTO_SPHERES)) ? 1 : 0,
+                          nullptr, nullptr, nullptr, 0u, c->rank, c->world, nullptr, nullptr, 0, 0, 0, 0};
+}
+
 // One render launch of the selected kernel over the packed rows [f.row0, f.row0 + f.rows).
 // stream / counter_pair: the stream to launch on and which tile-counter pair the wavefront kernel uses (bands that may
 // run concurrently need their own).
@@ -546,10 +556,7 @@ int launch_kernel(rt_b200_ctx *c, const rt::FrameParams &f, cudaStream_t stream,
             CUDA_TRY(cudaMemsetAsync(c->d_tile_counter, 0, 2 * RT_MAX_BANDS * sizeof(unsigned long long), stream));
             c->tile_counter_dirty = false;
         }
-        rt::WaveLaunch wl{c->d_tile_counter + 2 * counter_pair, c->d_cubic_mask, c->sphere_r2_max, c->shadow_cache, c->wave_variant, c->cubic_filter,
-                          (c->cull_backfacing && c->cull_safe) ? 1 : 0,
-                          (c->accel > 0 || (c->accel < 0 && c->view.n_sphere >= RT_GRID_AUTO_SPHERES)) ? 1 : 0,
-                          nullptr, nullptr, nullptr, 0u, c->rank, c->world, nullptr, nullptr, 0, 0, 0, 0};
+        rt::WaveLaunch wl = wave_launch_of(c, counter_pair);
         if (c->sync_in_kernel) {   // fused gather: the render kernel does the frame hand-shake itself
             wl.sync_go = c->d_go;
             wl.sync_flags = c->d_flags;
@@ -559,7 +566,7 @@ int launch_kernel(rt_b200_ctx *c, const rt::FrameParams &f, cudaStream_t stream,
                 wl.dyn_counters = c->d_tiles;
                 wl.dyn_slot_group = c->d_slot_group;
                 wl.dyn_n_groups = c->dyn_n_groups;
-                wl.dyn_group_rows = RT_DYN_GROUP_ROWS;
+                wl.dyn_group_rows = c->dyn_group_rows;
                 wl.dyn_max_slots = c->dyn_max_slots;
                 wl.dyn_ahead = RT_DYN_AHEAD;
             }
@@ -680,8 +687,14 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
     // the WHOLE image (as a single-rank frame) and its CTAs pull tiles from the job's counter in rank 0's memory.
     c->dynamic_now = c->sync_in_kernel && c->dynamic_tiles && c->d_tiles != nullptr;
     if (c->dynamic_now) {
-        if (!c->d_slot_group) {
-            c->dyn_n_groups = (c->height + RT_DYN_GROUP_ROWS - 1) / RT_DYN_GROUP_ROWS;
+        // groups of one tile height of rows (8; 16 for the 512-thread variant): re-made when the variant changes
+        const int group_rows = rt::wave_tile_rows(c->view, wave_launch_of(c, 0));
+        if (!c->d_slot_group || group_rows != c->dyn_group_rows) {
+            CUDA_TRY(cudaStreamSynchronize(c->stream));
+            cudaFree(c->d_slot_group);
+            c->d_slot_group = nullptr;
+            c->dyn_group_rows = group_rows;
+            c->dyn_n_groups = (c->height + group_rows - 1) / group_rows;
             c->dyn_max_slots = c->dyn_n_groups + RT_DYN_AHEAD + 1;
             CUDA_TRY(cudaMalloc((void **) &c->d_slot_group, sizeof(int) * (size_t) c->dyn_max_slots));
             CUDA_TRY(rt::launch_dyn_table_init(c->d_slot_group, c->dyn_max_slots, RT_DYN_AHEAD, c->dyn_n_groups, c->rank, c->world, c->stream));
@@ -691,7 +704,7 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
         f.world = 1;
         f.local_rows = c->height;
         band_start[0] = 0;
-        band_start[1] = c->dyn_n_groups * RT_DYN_GROUP_ROWS;   // whole groups (rows past the image are masked by local_rows);
+        band_start[1] = c->dyn_n_groups * c->dyn_group_rows;   // whole groups (rows past the image are masked by local_rows);
                                                                // n_bands == 1: the fused gather never streams
     }
     if (shared && c->flag_barrier) {

@@ -32,4 +32,15 @@ cudaError_t launch_render_wave(const SceneView &scene, const FrameParams &frame,
                              : launch_render_wave_plain(scene, frame, wl, stream);
 }
 
+// Tile height (rows) of the variant launch_render_wave will use: the dynamic split hands out row groups that are a
+// multiple of it.
+int wave_tile_rows(const SceneView &scene, const WaveLaunch &wl)
+{
+    int dev = 0, max_smem = 0, sm_smem = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 16;
+    cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    cudaDeviceGetAttribute(&sm_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
+    return wave_pick_variant(scene, wl, max_smem, sm_smem) == 5 ? 16 : 8;
+}
+
 } // namespace rt

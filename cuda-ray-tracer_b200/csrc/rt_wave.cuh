@@ -66,7 +66,6 @@ struct WaveCtl {
     int occ_found[2];            // occluders found so far by [0] the sphere pass, [1] the cubic pass
     int prim_rays, prim_hits;    // recent primary rays / hits of this CTA (decayed): the cubic filter runs on primary
     int prim_filter;             // rays only while enough of them miss for a proven miss to pay for the filter
-    unsigned chunk_next, chunk_end;   // tiles already pulled from the counter and not rendered yet (thread 0 only)
     int dyn_slot, dyn_group;     // dynamic ownership: the last slot -> group lookup (thread 0 only)
     double cam_x[32], cam_y[MAX_WARPS];   // camera-plane coordinates of the current tile's 32 columns / W/32 rows
 };
@@ -103,8 +102,14 @@ struct WaveDyn {
     int n_groups, group_rows, max_slots, ahead;
 };
 
+// q = n / d for n * d < 2^32 with inv = ceil(2^32 / d) (d >= 2; d == 1 is passed as inv = 0)
+__host__ __device__ inline unsigned magic_inv(unsigned d) { return d > 1u ? 0xffffffffu / d + 1u : 0u; }
+__device__ __forceinline__ unsigned magic_div(unsigned n, unsigned inv) { return inv ? __umulhi(n, inv) : n; }
+
 struct WaveConfig {
     int tiles_x, tiles_y;        // 32 x (W/32) pixel tiles over [local_rows][width]
+    unsigned inv_tiles_x;        // magic_inv(tiles_x): tile -> (column, row) without an integer division per thread
+    unsigned tiles_per_group, inv_tiles_per_group;   // dynamic ownership: tiles in one row group
     int spheres_in_smem;
     int use_shadow_cache;
     int use_cubic_filter;

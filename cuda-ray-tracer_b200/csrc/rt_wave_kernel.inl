@@ -26,39 +26,30 @@ __device__ __forceinline__ void store_primary(uchar4 *out, size_t index, bool fi
 // Static split: this GPU's counter counts the tiles of its own strips.  Dynamic ownership (WaveDyn): the counter
 // counts tiles of SLOTS; the slot's row group comes from the table, which is filled `ahead` slots in advance from the
 // job's counter in rank 0's memory.
-// The counter's round trip (~0.5 us to L2 and back, with the whole CTA waiting at the barrier behind it) is paid once
-// per CHUNK of tiles: up to four while plenty of tiles are left, one near the end of the frame (guided self-scheduling:
-// remaining / (8 x CTAs)), so the tail of the frame is as fine-grained as before.
+// (Measured in round 2 and dropped: pulling several tiles per atomic, pulling the next tile one wave ahead — no gain on
+// one GPU, the other CTAs of the SM cover the round trip, and a coarser tail on several — and a warp-collective
+// variant that pre-reads the slot table while the atomic is in flight: 2 us per frame better with the dynamic split,
+// 1 % worse without.)
 __device__ __forceinline__ int next_tile_index(const WaveConfig &cfg, WaveCtl &ctl, int n_tiles, int tile_rows)
 {
-    if (ctl.chunk_next == ctl.chunk_end) {
-        // tiles this GPU still expects to hand out: of its own strips (static) or of an equal share of the image (dynamic)
-        const unsigned pulled = ctl.chunk_end;   // a lower bound of the counter
-        const unsigned share = cfg.dyn.counters != nullptr ? (unsigned) n_tiles / (unsigned) cfg.sync.world : (unsigned) n_tiles;
-        const unsigned left = share > pulled ? share - pulled : 0u;
-        unsigned want = left / (8u * gridDim.x);
-        want = want < 1u ? 1u : (want > 4u ? 4u : want);
-        const unsigned t = atomicAdd(reinterpret_cast<unsigned *>(cfg.tile_counter), want);
-        ctl.chunk_next = t;
-        ctl.chunk_end = t + want;
-    }
-    const unsigned t = ctl.chunk_next++;
+    const unsigned t = atomicAdd(reinterpret_cast<unsigned *>(cfg.tile_counter), 1u);
     if (cfg.dyn.counters == nullptr) return t < (unsigned) n_tiles ? (int) t : n_tiles;
-    const unsigned tiles_per_group = (unsigned) (cfg.tiles_x * (cfg.dyn.group_rows / tile_rows));
-    const unsigned k = t / tiles_per_group, r = t - k * tiles_per_group;
+    const unsigned tiles_per_group = cfg.tiles_per_group;
+    const unsigned k = magic_div(t, cfg.inv_tiles_per_group), r = t - k * tiles_per_group;   // t * tiles_per_group < 2^32
     if (k >= (unsigned) cfg.dyn.max_slots) return n_tiles;      // cannot happen before the end marker has been seen
     if (r == 0u && k + cfg.dyn.ahead < (unsigned) cfg.dyn.max_slots) {
         // first tile of slot k: fetch the group of slot k + ahead (groups 0 .. world * ahead - 1 were assigned statically)
         const unsigned got = atomicAdd_system(reinterpret_cast<unsigned *>(cfg.dyn.counters + (cfg.sync.seq & 1u)), 1u);
         const long long grp = (long long) got + (long long) cfg.sync.world * cfg.dyn.ahead;
         const int val = grp < cfg.dyn.n_groups ? (int) grp : -2;
-        asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(cfg.dyn.slot_group + k + cfg.dyn.ahead), "r"(val) : "memory");
+        // relaxed: the group number is the whole message (an acquire on the reading side would flush the SM's L1 per tile)
+        asm volatile("st.relaxed.gpu.global.s32 [%0], %1;" ::"l"(cfg.dyn.slot_group + k + cfg.dyn.ahead), "r"(val) : "memory");
     }
     int grp = ctl.dyn_group;
     if (ctl.dyn_slot != (int) k) {      // one table look-up per slot and CTA, not per tile
         const long long t0 = clock64();
         for (;;) {
-            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(grp) : "l"(cfg.dyn.slot_group + k) : "memory");
+            asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(grp) : "l"(cfg.dyn.slot_group + k) : "memory");
             if (grp != -1) break;
             if (clock64() - t0 > 40000000000LL) {   // ~20 s: report instead of hanging the box
                 *cfg.sync.timed_out = 1u;
@@ -71,8 +62,8 @@ __device__ __forceinline__ int next_tile_index(const WaveConfig &cfg, WaveCtl &c
         ctl.dyn_group = grp;
     }
     if (grp < 0) return n_tiles;
-    const unsigned tile_row = (unsigned) grp * (unsigned) (cfg.dyn.group_rows / tile_rows) + r / (unsigned) cfg.tiles_x;
-    return (int) (tile_row * (unsigned) cfg.tiles_x + r % (unsigned) cfg.tiles_x);
+    // the group's tiles in the frame's tile space: group g covers tile rows [g * h, (g + 1) * h), h = group_rows / tile_rows
+    return (int) ((unsigned) grp * tiles_per_group + r);
 }
 
 __device__ __forceinline__ float blend(float out, float ratio, float c) { return (1.0f - ratio) * out + ratio * c; }
@@ -136,7 +127,6 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
             ctl.occ_found[0] = ctl.occ_found[1] = 0;
             ctl.prim_rays = ctl.prim_hits = 0;
             ctl.prim_filter = 1;
-            ctl.chunk_next = ctl.chunk_end = 0u;
             ctl.dyn_slot = -1;
             ctl.dyn_group = -1;
         }
@@ -223,7 +213,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         }
         if (tile >= 0 && tid < TILE_W + TILE_ROWS) {
             // the two divisions of primary ray generation (update-cpu.cpp:84-87) once per column / row of the tile
-            const int tx = tile % cfg.tiles_x, ty = tile / cfg.tiles_x;
+            const int ty = (int) magic_div((unsigned) tile, cfg.inv_tiles_x), tx = tile - ty * cfg.tiles_x;
             if (tid < TILE_W) {
                 ctl.cam_x[tid] = primary_cam_x(f, tx * TILE_W + tid);
             }
@@ -241,7 +231,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         int bounces = 0, pixel = 0;
         const bool primary = tile >= 0;
         if (primary) {
-            const int tx = tile % cfg.tiles_x, ty = tile / cfg.tiles_x;
+            const int ty = (int) magic_div((unsigned) tile, cfg.inv_tiles_x), tx = tile - ty * cfg.tiles_x;
             const int x = tx * TILE_W + (warp % WX) * 8 + (lane & 7);
             const int lrow = f.row0 + ty * TILE_ROWS + (warp / WX) * 4 + (lane >> 3);
             const int y = local_to_image_row(lrow, f.strip_rows, f.rank, f.world);
@@ -517,6 +507,10 @@ cudaError_t launch_wave_variant(const SceneView &scene, const FrameParams &frame
     const size_t smem = wave_fixed_smem<W>() + scene_smem + wave_cubic_smem(scene, W);
     cfg.tiles_x = (frame.width + TileGeom<W>::TILE_W - 1) / TileGeom<W>::TILE_W;
     cfg.tiles_y = (frame.rows + TileGeom<W>::TILE_ROWS - 1) / TileGeom<W>::TILE_ROWS;
+    if ((unsigned long long) cfg.tiles_x * cfg.tiles_y * (unsigned long long) cfg.tiles_x >= (1ULL << 32)) return cudaErrorInvalidConfiguration;
+    cfg.inv_tiles_x = magic_inv((unsigned) cfg.tiles_x);
+    cfg.tiles_per_group = (unsigned) (cfg.tiles_x * (cfg.dyn.group_rows > 0 ? cfg.dyn.group_rows / TileGeom<W>::TILE_ROWS : 1));
+    cfg.inv_tiles_per_group = magic_inv(cfg.tiles_per_group);
     int per_sm = 1;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W, smem);
     if (e != cudaSuccess) return e;
@@ -554,6 +548,18 @@ cudaError_t RT_WAVE_GRID_TU(const SceneView &scene, const FrameParams &frame, co
 #endif
 
 namespace {
+
+// The variant launch_render_wave_t will pick for this scene: the host needs the tile height before the launch.
+inline int wave_pick_variant(const SceneView &scene, const WaveLaunch &wl, int max_smem, int sm_smem)
+{
+    const bool grid = wl.accel && scene.grid.cell_start != nullptr && scene.n_sphere > 0;
+    if (grid) return wl.variant == 3 ? 3 : 2;
+    if (wl.variant > 0) return wl.variant;
+    size_t scene_smem = wave_scene_smem(scene, true);
+    if (wave_fixed_smem<512>() + scene_smem + wave_cubic_smem(scene, 512) > (size_t) max_smem) scene_smem = wave_scene_smem(scene, false);
+    const size_t cta256 = wave_fixed_smem<256>() + scene_smem + wave_cubic_smem(scene, 256) + 1024;
+    return (3 * cta256 <= (size_t) sm_smem) ? 3 : 5;
+}
 
 template <bool CUBIC>
 cudaError_t launch_render_wave_t(const SceneView &scene, const FrameParams &frame, const WaveLaunch &wl, cudaStream_t stream)
