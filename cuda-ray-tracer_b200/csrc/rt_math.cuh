@@ -203,6 +203,31 @@ __device__ __forceinline__ d3 surface_normal(const double *__restrict__ k, const
     return normalize3(g);
 }
 
+// Per-class gradients: surface_normal() restricted to the coefficients a class can have.  The terms left out are
+// products with coefficients that are exactly 0, i.e. +-0 added to the sums: the gradient — and with it the normal —
+// is the same number; only the sign of a component that is exactly zero may differ, which nothing downstream can see
+// (x + (+-0) = x, (+-0) * y adds +-0 to a dot product, and the shading factor compares with 0).
+//   plane   (only x, y, z, c):  grad F = (x, y, z), the same at every point: normalised once per CTA
+//   sphere  (x2 = y2 = z2 = 1): grad F = 2 p + (x, y, z)       — 2.0 * 1.0 * p.x == 2.0 * p.x
+//   quadric (degree <= 2)
+__device__ __forceinline__ d3 sphere_gradient(const double4 k, const d3 &p)
+{
+    return d3{2.0 * p.x + k.x, 2.0 * p.y + k.y, 2.0 * p.z + k.z};
+}
+
+// q = {x2,y2,z2,xy,xz,yz,x,y,z,c}; association as in surface_normal: (2 k2 p + l) + (p_b k_ab + p_c k_ac)
+__device__ __forceinline__ d3 quadric_gradient(const double *__restrict__ q, const d3 &p)
+{
+    d3 g;
+    g.x = 2.0 * q[0] * p.x + q[6];
+    g.y = 2.0 * q[1] * p.y + q[7];
+    g.z = 2.0 * q[2] * p.z + q[8];
+    g.x += p.y * q[3] + p.z * q[4];
+    g.y += p.x * q[3] + p.z * q[5];
+    g.z += p.x * q[4] + p.y * q[5];
+    return g;
+}
+
 // light_impl.h:17-27: direction rounded to float and widened again; max_t = 1 (point) or 1e6
 __device__ __forceinline__ d3 shadow_dir(const LightDev &l, const d3 &p, double &max_t)
 {

@@ -26,6 +26,7 @@ struct TileGeom {
 // Scene arrays staged once per CTA into shared memory (SoA by class, rt_scene.h).
 struct SceneSmem {
     const double4 *plane;
+    const d3 *plane_n;           // [n_plane] unit normals: a plane's gradient is the same at every point
     const float4 *sphere_f;      // shared or global, see WaveConfig::spheres_in_smem
     const double *quadric;
     const double *cubic;
@@ -131,7 +132,7 @@ __host__ __device__ inline size_t wave_fixed_smem()
 
 __host__ __device__ inline size_t wave_scene_smem(const SceneView &sc, bool spheres)
 {
-    return align16(sizeof(double4) * sc.n_plane) + (spheres ? align16(sizeof(float4) * sc.n_sphere) : 0) +
+    return align16(sizeof(double4) * sc.n_plane) + align16(sizeof(d3) * sc.n_plane) + (spheres ? align16(sizeof(float4) * sc.n_sphere) : 0) +
            align16(sizeof(double) * 10 * sc.n_quadric) + align16(sizeof(double) * 20 * sc.n_cubic) +
            align16(sizeof(unsigned) * sc.n_cubic) + align16(sizeof(float) * RT_CF_FLOATS * sc.n_cubic) +
            align16(sizeof(LightDev) * sc.n_lights);

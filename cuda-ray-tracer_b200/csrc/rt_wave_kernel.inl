@@ -94,6 +94,13 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         sp += align16(sizeof(double4) * g.n_plane);
         for (int i = tid; i < g.n_plane; i += WAVE) pl[i] = g.plane[i];
         s.plane = pl;
+        d3 *pn = reinterpret_cast<d3 *>(sp);
+        sp += align16(sizeof(d3) * g.n_plane);
+        for (int i = tid; i < g.n_plane; i += WAVE) {
+            const double4 k = g.plane[i];
+            pn[i] = normalize3(d3{k.x, k.y, k.z});
+        }
+        s.plane_n = pn;
         if (cfg.spheres_in_smem) {
             float4 *sf = reinterpret_cast<float4 *>(sp);
             sp += align16(sizeof(float4) * g.n_sphere);
@@ -269,7 +276,20 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
             if (h.slot >= 0) {
                 obj = h.orig;
                 const d3 p = d3{o.x + h.t * d.x, o.y + h.t * d.y, o.z + h.t * d.z};
-                const d3 n = surface_normal(g.coef_full + 20 * obj, p);
+                // normal_vector() (surface_impl.h:157-172).  Kernels without the cubic class evaluate only the coefficients
+                // the hit object's class can have (rt_math.cuh: *_gradient).  The kernels with it keep the full formula for
+                // every class: the class branches cost them more than they save (measured: +1 % on the four single-cubic
+                // scenes; a mask-driven gradient for the cubic class itself +3 % on clebsch).
+                d3 n;
+                if (!CUBIC) {
+                    int sl = h.slot;
+                    if (sl < g.n_plane) n = s.plane_n[sl];
+                    else if ((sl -= g.n_plane) < g.n_sphere) n = normalize3(sphere_gradient(g.sphere[sl], p));
+                    else n = normalize3(quadric_gradient(s.quadric + 10 * (sl - g.n_sphere), p));
+                }
+                else {
+                    n = surface_normal(g.coef_full + 20 * obj, p);
+                }
                 wh.px[tid] = p.x; wh.py[tid] = p.y; wh.pz[tid] = p.z;
                 wh.nx[tid] = n.x; wh.ny[tid] = n.y; wh.nz[tid] = n.z;
                 wh.occluded[tid] = 0u;
