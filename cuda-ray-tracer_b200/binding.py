@@ -18,7 +18,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "librt_b200.so")
+LIB_PATH = os.environ.get("RT_B200_LIB", os.path.join(HERE, "librt_b200.so"))   # (override: A/B experiments)
 
 COUNTER_FIELDS = ("primary_rays", "reflection_rays", "shadow_rays", "hits", "lit",
                   "tests_plane", "tests_sphere", "tests_quadric", "tests_cubic", "fp64_confirms", "cubic_exact")
