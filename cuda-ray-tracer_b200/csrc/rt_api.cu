@@ -206,7 +206,9 @@ struct rt_b200_ctx {
     bool cull_safe = true;           // every light / object colour is finite and moderate: 0 * colour is exactly 0
     bool buffers_dirty = true;
 
-    int kernel_kind = 1;
+    int kernel_kind = 1;             // option "kernel"
+    bool wave_fits = true;           // the wavefront kernel's per-CTA scene copy fits shared memory (else kernel 0 renders)
+    int kernel_now() const { return (kernel_kind == 1 && !wave_fits) ? 0 : kernel_kind; }
     int launches = 0;                // render launches of the last update
     bool count = true;
     bool rendered = false;
@@ -520,6 +522,7 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     v.lights = c->d_lights;
     v.sphere_center_max = center_max;
 
+    c->wave_fits = rt::wave_scene_fits(v);
     rc = build_grid(c, 0.0);
     if (rc == RT_B200_OK) rc = ensure_buffers(c);
     if (rc != RT_B200_OK) {
@@ -548,7 +551,7 @@ rt::WaveLaunch wave_launch_of(const rt_b200_ctx *c, int counter_pair)
 // run concurrently need their own).
 int launch_kernel(rt_b200_ctx *c, const rt::FrameParams &f, cudaStream_t stream, int counter_pair)
 {
-    if (c->kernel_kind == 0) {
+    if (c->kernel_now() == 0) {
         CUDA_TRY(rt::launch_render_exact(c->view, f, stream));
     }
     else {
@@ -682,7 +685,7 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
     if (c->count) CUDA_TRY(cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long) * rt::CNT_COUNT, c->stream));
     CUDA_TRY(cudaEventRecord(c->ev_start, c->stream));
     // kernel 1 does the go / flag hand-shake of the fused gather in its own prologue / epilogue: no extra launches
-    c->sync_in_kernel = shared && c->flag_barrier && c->kernel_kind == 1;
+    c->sync_in_kernel = shared && c->flag_barrier && c->kernel_now() == 1;
     // Dynamic tile ownership: the frame is one tile space for all GPUs; this rank's launch describes
     // the WHOLE image (as a single-rank frame) and its CTAs pull tiles from the job's counter in rank 0's memory.
     c->dynamic_now = c->sync_in_kernel && c->dynamic_tiles && c->d_tiles != nullptr;
@@ -715,7 +718,7 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
         }
     }
     c->launches = 0;
-    const bool overlap = streamed && n_bands > 1 && c->band_overlap && c->kernel_kind == 1 && !c->tile_counter_dirty;
+    const bool overlap = streamed && n_bands > 1 && c->band_overlap && c->kernel_now() == 1 && !c->tile_counter_dirty;
     for (int b = 0; b < n_bands; b++) {
         f.row0 = band_start[b];
         f.rows = band_start[b + 1] - band_start[b];

@@ -31,6 +31,7 @@ struct WaveLaunch {
 // (re)initialise a slot -> group table: the first `ahead` slots statically, the rest "not fetched yet"
 cudaError_t launch_dyn_table_init(int *slot_group, int max_slots, int ahead, int n_groups, int rank, int world, cudaStream_t stream);
 cudaError_t launch_render_wave(const SceneView &scene, const FrameParams &frame, const WaveLaunch &wl, cudaStream_t stream);
+bool wave_scene_fits(const SceneView &scene);   // false: too many lights / quadrics / cubics for the per-CTA scene copy
 int wave_tile_rows(const SceneView &scene, const WaveLaunch &wl);   // 8 or 16: tile height of the variant that launch would use
 
 // Undo the strip interleave after the all-gather: gathered = [world][local_rows][width] -> frame[height][width].

@@ -32,6 +32,18 @@ cudaError_t launch_render_wave(const SceneView &scene, const FrameParams &frame,
                              : launch_render_wave_plain(scene, frame, wl, stream);
 }
 
+// Does the wavefront kernel's per-CTA copy of the scene (planes, quadrics, cubics + filter tables, lights; the sphere
+// filter array falls back to global memory on its own) fit the device's shared memory?  The limits are a few thousand
+// lights or quadrics, a few hundred cubics.  When it does not, rt_api.cu renders with the exact per-pixel kernel, which
+// reads the scene from global memory and has no such limit — the reference accepts any object and light count.
+bool wave_scene_fits(const SceneView &scene)
+{
+    int dev = 0, max_smem = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return false;
+    cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    return wave_fixed_smem<256>() + wave_scene_smem(scene, false) + wave_cubic_smem(scene, 256) <= (size_t) max_smem;
+}
+
 // Tile height (rows) of the variant launch_render_wave will use: the dynamic split hands out row groups that are a
 // multiple of it.
 int wave_tile_rows(const SceneView &scene, const WaveLaunch &wl)

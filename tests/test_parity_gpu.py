@@ -306,6 +306,48 @@ def test_shared_host_frame_ranks_as_processes(pkg, rt, scenes_dir, tmp_path, wor
         rt.host_free_shared(ptr)
 
 
+def test_scenes_larger_than_shared_memory(pkg, rt, oracle):
+    """The wavefront kernel keeps planes, quadrics, cubics and lights in shared memory; scenes beyond that (thousands of
+    lights or quadrics) must still render — the reference takes any count (update-cpu.cpp:48-76) — through the exact
+    kernel, and match the oracle."""
+    from cuda_ray_tracer_b200 import camera
+    from cuda_ray_tracer_b200 import scene as S
+    bg = np.array([0.05, 0.1, 0.2], dtype=np.float32)
+    rng = np.random.default_rng(3)
+    obj = lambda k, refl=0.0, col=(0.8, 0.6, 0.2): S.make_object(k, refl, col)
+    m = camera.TEST_POSES["identity"]
+    # 6000 lights (240 KB of light records) over two spheres and a mirror plane
+    sc = S.Scene(48, 32, np.radians(55.0), bg, 2)
+    sc.objects = np.array([obj(S.surface_sphere([0, 0, 8], 2.0), 0.2), obj(S.surface_sphere([2.5, 1, 7], 0.8), 0.0, (0.2, 0.9, 0.3)),
+                           obj(S.surface_plane([0, -2.5, 0], [0, 1, 0]), 0.3, (0.5, 0.5, 0.5))], dtype=S.OBJECT_DTYPE)
+    ls = []
+    for i in range(6000):
+        v = rng.normal(size=3)
+        ls.append(S.light_spherical(0.2, list(6.0 * v + np.array([0.0, 6.0, 4.0])), [1, 0.9, 0.8]) if i % 2
+                  else S.light_directional(0.001, list(v), [0.8, 0.9, 1.0]))
+    sc.lights = np.array(ls, dtype=S.LIGHT_DTYPE)
+    with rt.Renderer(sc) as r:
+        r.update(m)
+        assert_parity(r.gather(), oracle.quantize_rgba8(oracle.PortOracle(sc).render(m, threads=os.cpu_count())), "6000 lights")
+    # 3500 quadrics (280 KB of coefficients): small ellipsoids on a lattice
+    sc = S.Scene(64, 40, np.radians(55.0), bg, 1)
+    objs = []
+    for i in range(3500):
+        c = np.array([(i % 50) - 25.0, ((i // 50) % 10) - 5.0, 30.0 + 2.0 * (i // 500)]) * 0.9
+        a, b, cc = rng.uniform(2.0, 6.0, 3)
+        k = np.zeros(20)
+        k[10], k[11], k[12] = a, b, cc                                   # a x^2 + b y^2 + c z^2 ...
+        k[16], k[17], k[18] = -2 * a * c[0], -2 * b * c[1], -2 * cc * c[2]
+        k[19] = a * c[0] ** 2 + b * c[1] ** 2 + cc * c[2] ** 2 - 1.0     # ... = 1 around c
+        objs.append(obj(k, 0.0, tuple(rng.uniform(0.2, 0.9, 3))))
+    sc.objects = np.array(objs, dtype=S.OBJECT_DTYPE)
+    sc.lights = np.array([S.light_directional(2.0, [0.3, -1, 0.5], [1, 1, 1]), S.light_spherical(3000.0, [0, 10, 0], [1, 1, 1])], dtype=S.LIGHT_DTYPE)
+    with rt.Renderer(sc) as r:
+        assert r.class_counts()["quadric"] == 3500
+        r.update(m)
+        assert_parity(r.gather(), oracle.quantize_rgba8(oracle.PortOracle(sc).render(m, threads=os.cpu_count())), "3500 quadrics")
+
+
 def test_contexts_on_several_devices_in_one_process(pkg, rt, scenes_dir):
     """One process, one context per device (rt_b200.h allows a thread per GPU): the >48 KB dynamic shared memory
     attribute of the render kernels is per DEVICE, so the second device must get it too; and the same-process fused
