@@ -28,7 +28,14 @@ def _stale() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, checked: bool = False) -> str:
+    """checked=True: librt_b200_checked.so with -DRT_B200_CHECKED (index assertions in the kernels, rt_wave.cuh: RT_CHECK)."""
+    if checked:
+        out = os.path.join(HERE, "librt_b200_checked.so")
+        nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+        subprocess.run([nvcc] + NVCC_FLAGS + ["-DRT_B200_CHECKED", "-shared", "-o", out] +
+                       [os.path.join(CSRC, s) for s in SOURCES] + ["-ldl"], check=True)
+        return out
     if not force and not _stale():
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
@@ -39,4 +46,4 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, checked="--checked" in sys.argv))

@@ -2,12 +2,30 @@
 #ifndef RT_WAVE_CUH
 #define RT_WAVE_CUH
 
+#include <cstdio>
+
 #include "rt_cubic.cuh"
 #include "rt_cubic_filter.cuh"
 #include "rt_filter.cuh"
 #include "rt_trace.cuh"
 
 namespace rt {
+
+// Checked build (build.py --checked -> librt_b200_checked.so): every index into the ray pool, the hit records, the slot
+// table and the frame is asserted in range; a violation prints its source line and traps, which the host sees as a
+// failed launch.  The GPU tests run against that library too (tools/gpu_checked.sh).  compute-sanitizer is closed on
+// this pool (profiles/r2_compute_sanitizer_closed.log), so these are the bounds checks there are.
+#ifdef RT_B200_CHECKED
+#define RT_CHECK(cond)                                                                                    \
+    do {                                                                                                  \
+        if (!(cond)) {                                                                                    \
+            printf("RT_CHECK failed: %s  (%s:%d, block %d thread %d)\n", #cond, __FILE__, __LINE__, (int) blockIdx.x, (int) threadIdx.x); \
+            __trap();                                                                                     \
+        }                                                                                                 \
+    } while (0)
+#else
+#define RT_CHECK(cond) ((void) 0)
+#endif
 
 constexpr int LIGHT_CHUNK = 32;  // lights handled per visibility word
 constexpr int MAX_WARPS = 16;    // largest CTA: 512 threads

@@ -36,7 +36,9 @@ __device__ __forceinline__ int next_tile_index(const WaveConfig &cfg, WaveCtl &c
     if (cfg.dyn.counters == nullptr) return t < (unsigned) n_tiles ? (int) t : n_tiles;
     const unsigned tiles_per_group = cfg.tiles_per_group;
     const unsigned k = magic_div(t, cfg.inv_tiles_per_group), r = t - k * tiles_per_group;   // t * tiles_per_group < 2^32
-    if (k >= (unsigned) cfg.dyn.max_slots) return n_tiles;      // cannot happen before the end marker has been seen
+    // past the table: the CTAs' last pulls overshoot the counter (one each); every slot that can hold a group lies below
+    // max_slots = n_groups + ahead + 1 and has been handed out completely by then
+    if (k >= (unsigned) cfg.dyn.max_slots) return n_tiles;
     if (r == 0u && k + cfg.dyn.ahead < (unsigned) cfg.dyn.max_slots) {
         // first tile of slot k: fetch the group of slot k + ahead (groups 0 .. world * ahead - 1 were assigned statically)
         const unsigned got = atomicAdd_system(reinterpret_cast<unsigned *>(cfg.dyn.counters + (cfg.sync.seq & 1u)), 1u);
@@ -62,6 +64,7 @@ __device__ __forceinline__ int next_tile_index(const WaveConfig &cfg, WaveCtl &c
         ctl.dyn_group = grp;
     }
     if (grp < 0) return n_tiles;
+    RT_CHECK(grp < cfg.dyn.n_groups && (unsigned) grp * tiles_per_group + r < (unsigned) n_tiles);
     // the group's tiles in the frame's tile space: group g covers tile rows [g * h, (g + 1) * h), h = group_rows / tile_rows
     return (int) ((unsigned) grp * tiles_per_group + r);
 }
@@ -258,6 +261,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
             active = tid < take;
             if (active) {
                 const int r = base + tid;
+                RT_CHECK(r >= 0 && r < 2 * WAVE);
                 o = d3{pool.ox[r], pool.oy[r], pool.oz[r]};
                 d = d3{pool.dx[r], pool.dy[r], pool.dz[r]};
                 out_r = pool.out_r[r]; out_g = pool.out_g[r]; out_b = pool.out_b[r];
@@ -313,6 +317,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
             __syncthreads();
             int base = 0;
             for (int w = 0; w < warp; w++) base += ctl.warp_base[w];
+            RT_CHECK(!hit || base + __popc(m & ((1u << lane) - 1u)) < WAVE);
             if (hit) wh.hitlist[base + __popc(m & ((1u << lane) - 1u))] = (unsigned short) tid;
             if (tid == WAVE - 1) ctl.n_hits = base + __popc(m);
         }
@@ -343,7 +348,9 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
             const bool lone_cubic = CUBIC && s.hit_o != nullptr && cfg.use_cubic_filter && g.n_objects == 1;
             for (int task = tid; task < n_hits * lc; task += WAVE) {
                 const int j = n_hits > 1 ? (int) __umulhi((unsigned) task, inv_hits) : task;   // task / n_hits (task * n_hits < 2^32)
+                RT_CHECK(j >= 0 && j < lc && task - j * n_hits >= 0 && task - j * n_hits < n_hits);
                 const int k = wh.hitlist[task - j * n_hits];
+                RT_CHECK(k >= 0 && k < WAVE);
                 const LightDev l = s.lights[l0 + j];
                 const d3 p = d3{wh.px[k], wh.py[k], wh.pz[k]};
                 const d3 n = d3{wh.nx[k], wh.ny[k], wh.nz[k]};
@@ -441,6 +448,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
             wbase = __shfl_sync(0xffffffffu, wbase, 0);
             if (spawn) {
                 const int r = wbase + __popc(m & ((1u << lane) - 1u));
+                RT_CHECK(r >= 0 && r < 2 * WAVE);
                 pool.ox[r] = no.x; pool.oy[r] = no.y; pool.oz[r] = no.z;
                 pool.dx[r] = nd.x; pool.dy[r] = nd.y; pool.dz[r] = nd.z;
                 pool.out_r[r] = out_r; pool.out_g[r] = out_g; pool.out_b[r] = out_b;
@@ -450,6 +458,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
             }
         }
         // finished pixels leave the SM
+        RT_CHECK(!final_px || (pixel >= 0 && (size_t) pixel < (size_t) f.width * (size_t) (f.direct ? f.height : f.local_rows)));
         const uchar4 px = pack_rgba8(out_r, out_g, out_b);
         if (primary) store_primary(f.out, (size_t) pixel, final_px, px, vec_ok);
         else if (final_px) f.out[pixel] = px;

@@ -21,12 +21,15 @@ ap.add_argument("--height", type=int, default=2160)
 ap.add_argument("--bounces", type=int, default=4)
 ap.add_argument("--pose", default="initial")
 ap.add_argument("--accel", type=int, default=-1)
+ap.add_argument("--spheres", type=int, default=4096)
+ap.add_argument("--cubics", type=int, default=64)
+ap.add_argument("--lights", type=int, default=16)
 ap.add_argument("--count", type=int, default=0, help="1 = the counting instantiation of the kernel")
 ap.add_argument("--option", action="append", default=[], help="name=value, passed to rt_b200_set_option")
 a = ap.parse_args()
 if a.scene == "synthetic":
     from cuda_ray_tracer_b200 import synth
-    sc = synth.synthetic_scene(width=a.width, height=a.height)
+    sc = synth.synthetic_scene(n_spheres=a.spheres, n_cubics=a.cubics, n_lights=a.lights, width=a.width, height=a.height)
 else:
     sc = pkg.load_from_file(os.path.join(ROOT, "scenes", a.scene + ".yml")).with_overrides(
         width=a.width, height=a.height, max_reflections=a.bounces)
