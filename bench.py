@@ -568,8 +568,9 @@ def main():
                     "copies its strips into one shared host frame, or rank 0 gathers on the device and copies alone")
     ap.add_argument("--accel", type=int, default=0, choices=[-1, 0, 1], help="sphere-class grid (separate mode, SURVEY §8 f4): "
                     "0 = brute force like the reference (default, what the roofline is quoted on), 1 = on, -1 = library default")
-    ap.add_argument("--dynamic", type=int, default=1, choices=[0, 1], help="multi-GPU, fused gather: 1 = row groups of the image are "
-                    "handed out to the GPUs on demand by a counter in rank 0's memory (SURVEY §8 f3), 0 = static 8-row strips")
+    ap.add_argument("--dynamic", type=int, default=0, choices=[0, 1], help="multi-GPU, fused gather: 1 = row groups of the image are "
+                    "handed out to the GPUs on demand by a counter in rank 0's memory (SURVEY §8 f3), 0 = static 8-row strips (default: "
+                    "measured faster at 2, 4 and 8 GPUs, profiles/r2_scaling_8gpu.json)")
     ap.add_argument("--variant", type=int, default=0, help="wavefront kernel shape (0 = automatic)")
     ap.add_argument("--no-cull", dest="cull", action="store_false", help="trace every shadow ray the reference casts")
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -228,7 +228,8 @@ struct rt_b200_ctx {
     unsigned long long *d_tiles = nullptr;   // [2] behind go in rank 0's allocation: the job's group counters
     int *d_slot_group = nullptr;     // this GPU's slot -> group table
     int dyn_max_slots = 0, dyn_n_groups = 0, dyn_group_rows = 0;
-    int dynamic_tiles = 1;           // option: 1 = on (default), 0 = every rank renders its own strips
+    int dynamic_tiles = 0;           // option: 1 = on, 0 (default) = every rank renders its own strips — measured faster on the
+                                     // bundled frames at 2, 4 and 8 GPUs (profiles/r2_scaling_8gpu.json)
     bool dynamic_now = false;        // ... in effect for the frame being issued
     unsigned *h_timed_out = nullptr, *d_timed_out = nullptr;   // page-locked, mapped: the wait kernel's timeout report
     unsigned seq = 0;

@@ -175,7 +175,13 @@ int rt_b200_get_counters(rt_b200_ctx *ctx, rt_b200_counters *out);
  *                       on a scene's first streamed frames, keep the fastest, re-try another every 32nd frame
  *           "band_overlap"  rt_b200_update_to_host, wavefront kernel: 1 (default) = consecutive row bands alternate between
  *                       two streams, each with its own tile counter, so the tail of one band overlaps the start of the next
- *           "grid_density"  rebuild the grid at value / 100 cells per sphere (0 = default 1.5)                      */
+ *           "grid_density"  rebuild the grid at value / 100 cells per sphere (0 = default 1.5)
+ *           "dynamic_tiles" fused gather, wavefront kernel: 1 = the image is cut into groups of one
+ *                       tile height of rows that a counter in rank 0's memory hands out to the GPUs on demand (each GPU
+ *                       fetches two groups ahead over NVLink), so a GPU that finishes early takes more; 0 (default) =
+ *                       every rank renders its own interleaved strips.  Frames are identical; on the bundled scenes the
+ *                       static interleave is already balanced and measured 2-5 % faster (profiles/r2_scaling_8gpu.json)
+ *           "variant"   wavefront kernel shape: 0 = automatic, 2 / 3 = 256-thread CTAs, two / three per SM, 5 = 512 x 1 */
 int rt_b200_set_option(rt_b200_ctx *ctx, const char *name, int64_t value);
 
 /* Split timing of the last update, milliseconds: [0] render kernels, [1] gather (all-gather + unpack). */
