@@ -29,7 +29,8 @@ EXPORTS = ("rt_b200_upload_scene", "rt_b200_update", "rt_b200_gather", "rt_b200_
            "rt_b200_get_timing", "rt_b200_get_class_counts", "rt_b200_strip_layout", "rt_b200_version",
            "rt_b200_update_to_host", "rt_b200_frame_export", "rt_b200_frame_attach", "rt_b200_get_launches",
            "rt_b200_host_alloc", "rt_b200_host_free", "rt_b200_host_alloc_shared", "rt_b200_host_free_shared",
-           "rt_b200_get_grid_info", "rt_b200_band_layout", "rt_b200_frame_attach_peer")
+           "rt_b200_get_grid_info", "rt_b200_band_layout", "rt_b200_frame_attach_peer",
+           "rt_b200_render_no_alloc", "rt_b200_no_alloc_scratch_needed")
 
 UNIQUE_ID_BYTES = 128
 IPC_HANDLE_BYTES = 64
@@ -74,6 +75,9 @@ def load_library():
     L.rt_b200_frame_export.argtypes = [vp, vp]
     L.rt_b200_frame_attach.argtypes = [vp, vp]
     L.rt_b200_frame_attach_peer.argtypes = [vp, vp]
+    L.rt_b200_render_no_alloc.argtypes = [C.c_uint32, C.c_uint32, C.c_double, vp, C.c_uint32, vp, C.c_size_t, vp, C.c_size_t,
+                                          vp, C.c_int, vp, C.c_size_t, C.POINTER(C.c_float)]
+    L.rt_b200_no_alloc_scratch_needed.argtypes = [vp, C.c_size_t, C.c_size_t, C.POINTER(C.c_size_t)]
     L.rt_b200_get_launches.argtypes = [vp, C.POINTER(C.c_uint32)]
     L.rt_b200_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
     L.rt_b200_host_free.argtypes = [vp]
@@ -145,6 +149,31 @@ def host_view(ptr: int, height: int, width: int) -> np.ndarray:
     """uint8 [H, W, 4] view of a host frame at `ptr` (no copy)."""
     buf = (C.c_uint8 * (height * width * 4)).from_address(ptr)
     return np.frombuffer(buf, dtype=np.uint8).reshape(height, width, 4)
+
+
+NO_ALLOC_SCRATCH_BYTES = 1048576
+
+
+def no_alloc_scratch_needed(scene) -> int:
+    """Bytes of the library's static device scratch rt_b200_render_no_alloc needs for `scene` (host-only)."""
+    objs = np.ascontiguousarray(scene.objects)
+    n = C.c_size_t()
+    _check(load_library().rt_b200_no_alloc_scratch_needed(_dp(objs), len(objs), len(scene.lights), C.byref(n)))
+    return int(n.value)
+
+
+def render_no_alloc(scene, camera_matrix, device_ptr: int, nbytes: int, device: int = 0) -> float:
+    """rt_b200_render_no_alloc: one frame of `scene` into the caller's DEVICE buffer, no context and no allocation inside
+    the library (its scratch is a static __device__ array).  Returns the host-clock render time in ms."""
+    bg = np.ascontiguousarray(scene.bg_color, dtype=np.float32)
+    objs = np.ascontiguousarray(scene.objects)
+    lights = np.ascontiguousarray(scene.lights)
+    m = np.ascontiguousarray(camera_matrix, dtype=np.float64).reshape(16)
+    ms = C.c_float()
+    _check(load_library().rt_b200_render_no_alloc(int(scene.px_width), int(scene.px_height), float(scene.vertical_fov), _dp(bg),
+                                                  int(scene.max_reflections), _dp(objs), len(objs), _dp(lights), len(lights),
+                                                  _dp(m), int(device), C.c_void_p(device_ptr), int(nbytes), C.byref(ms)))
+    return ms.value
 
 
 class Renderer:

@@ -1280,3 +1280,257 @@ int rt_b200_band_layout(uint32_t rows, uint32_t n_bands, uint32_t unit, int tape
 }
 
 } // extern "C"
+
+// =====================================================================================================================
+// rt_b200_render_no_alloc — one frame without any allocation (include/rt_b200.h; no counterpart in the reference).
+// Nothing above this line is changed by it.
+//
+// The wavefront kernel's device scratch (tile counters + the class-sorted scene arrays it reads) lives in the static
+// array below instead of cudaMalloc'ed buffers.  In HOST code the array's name is only a host-side stand-in: its device
+// address comes from cudaGetSymbolAddress, once per device, with that device current (no_alloc_device_scratch).
+// =====================================================================================================================
+namespace {
+
+static __device__ __align__(256) unsigned char g_no_alloc_scratch[RT_B200_NO_ALLOC_SCRATCH_BYTES];
+
+// Host image of the scratch, built here and copied to the device in one transfer (static: no host allocation either).
+alignas(256) unsigned char g_no_alloc_host[RT_B200_NO_ALLOC_SCRATCH_BYTES];
+std::mutex g_no_alloc_mutex;                    // one call at a time: the staging area and the device array are shared
+constexpr int NO_ALLOC_MAX_DEVICES = 64;
+unsigned char *g_no_alloc_dev_ptr[NO_ALLOC_MAX_DEVICES] = {};   // device address of g_no_alloc_scratch per device ordinal
+
+// Offsets of the arrays inside the scratch (every array 256-byte aligned).
+struct NoAllocLayout {
+    size_t tile_counter, plane, sphere, sphere_f, quadric, cubic, cubic_mask, orig, coef_full, material, material_pi, lights;
+    size_t total;
+    size_t n_class[4];
+};
+
+size_t bump(size_t &at, size_t bytes)
+{
+    const size_t here = at;
+    at = (at + (bytes ? bytes : 1) + 255) & ~(size_t) 255;
+    return here;
+}
+
+NoAllocLayout no_alloc_layout(const void *objects, size_t n_objects, size_t n_lights)
+{
+    NoAllocLayout L{};
+    const char *obj_bytes = static_cast<const char *>(objects);
+    for (size_t i = 0; i < n_objects; i++) {
+        double k[20];
+        std::memcpy(k, obj_bytes + RT_B200_OBJECT_BYTES * i, 160);
+        L.n_class[classify(k)]++;
+    }
+    size_t at = 0;
+    L.tile_counter = bump(at, 2 * sizeof(unsigned long long));   // must start at zero: the host image carries the zeros
+    L.plane = bump(at, sizeof(double4) * L.n_class[rt::CLS_PLANE]);
+    L.sphere = bump(at, sizeof(double4) * L.n_class[rt::CLS_SPHERE]);
+    L.sphere_f = bump(at, sizeof(float4) * L.n_class[rt::CLS_SPHERE]);
+    L.quadric = bump(at, sizeof(double) * 10 * L.n_class[rt::CLS_QUADRIC]);
+    L.cubic = bump(at, sizeof(double) * 20 * L.n_class[rt::CLS_CUBIC]);
+    L.cubic_mask = bump(at, sizeof(unsigned) * L.n_class[rt::CLS_CUBIC]);
+    L.orig = bump(at, sizeof(int) * n_objects);
+    L.coef_full = bump(at, sizeof(double) * 20 * n_objects);
+    L.material = bump(at, sizeof(float4) * n_objects);
+    L.material_pi = bump(at, sizeof(float4) * n_objects);
+    L.lights = bump(at, sizeof(rt::LightDev) * n_lights);
+    L.total = at;
+    return L;
+}
+
+// Device address of the static scratch on `device` (current).  cudaGetSymbolAddress once per device.
+int no_alloc_device_scratch(int device, unsigned char **out)
+{
+    if (device >= 0 && device < NO_ALLOC_MAX_DEVICES && g_no_alloc_dev_ptr[device]) {
+        *out = g_no_alloc_dev_ptr[device];
+        return RT_B200_OK;
+    }
+    unsigned char *ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void **) &ptr, g_no_alloc_scratch);
+    if (e != cudaSuccess || ptr == nullptr)
+        return fail(RT_B200_ERR_CUDA, "cudaGetSymbolAddress(no-alloc scratch) on device %d: %s", device, cudaGetErrorString(e));
+    if (device >= 0 && device < NO_ALLOC_MAX_DEVICES) g_no_alloc_dev_ptr[device] = ptr;
+    *out = ptr;
+    return RT_B200_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int rt_b200_no_alloc_scratch_needed(const void *objects, size_t n_objects, size_t n_lights, size_t *bytes)
+{
+    if (!bytes || (n_objects && !objects)) return fail(RT_B200_ERR_ARG, "null argument");
+    if (n_objects > (size_t) 1 << 24 || n_lights > (size_t) 1 << 20) return fail(RT_B200_ERR_ARG, "scene too large");
+    *bytes = no_alloc_layout(objects, n_objects, n_lights).total;
+    return RT_B200_OK;
+}
+
+int rt_b200_render_no_alloc(uint32_t px_width, uint32_t px_height, double vertical_fov_rad, const float bg_color[3],
+                            uint32_t max_reflections, const void *objects, size_t n_objects, const void *lights,
+                            size_t n_lights, const double camera_matrix[16], int device, void *device_rgba8,
+                            size_t device_bytes, float *elapsed_ms)
+{
+    if (px_width == 0 || px_height == 0) return fail(RT_B200_ERR_ARG, "empty frame %ux%u", px_width, px_height);
+    if (!bg_color || !camera_matrix || !device_rgba8) return fail(RT_B200_ERR_ARG, "null argument");
+    if ((n_objects && !objects) || (n_lights && !lights)) return fail(RT_B200_ERR_ARG, "null scene array");
+    if (n_objects > (size_t) 1 << 24 || n_lights > (size_t) 1 << 20) return fail(RT_B200_ERR_ARG, "scene too large");
+    const size_t frame_bytes = sizeof(uchar4) * (size_t) px_width * px_height;
+    if (device_bytes < frame_bytes)
+        return fail(RT_B200_ERR_ARG, "device buffer holds %zu bytes, frame needs %zu", device_bytes, frame_bytes);
+    if (reinterpret_cast<uintptr_t>(device_rgba8) & 15u) return fail(RT_B200_ERR_ARG, "device buffer must be 16-byte aligned");
+    if ((unsigned long long) px_width * px_height >= (1ULL << 31)) return fail(RT_B200_ERR_ARG, "frame too large");
+
+    const NoAllocLayout L = no_alloc_layout(objects, n_objects, n_lights);
+    if (L.total > (size_t) RT_B200_NO_ALLOC_SCRATCH_BYTES)
+        return fail(RT_B200_ERR_ARG, "scene (%zu objects, %zu lights) needs %zu bytes of device scratch; rt_b200_render_no_alloc "
+                    "holds %d (use rt_b200_upload_scene / rt_b200_update for larger scenes)", n_objects, n_lights, L.total,
+                    RT_B200_NO_ALLOC_SCRATCH_BYTES);
+
+    int n_dev = 0;
+    CUDA_TRY(cudaGetDeviceCount(&n_dev));
+    if (device < 0 || device >= n_dev) return fail(RT_B200_ERR_CUDA, "no CUDA device %d (found %d)", device, n_dev);
+    CUDA_TRY(cudaSetDevice(device));
+    cudaPointerAttributes pa{};
+    if (cudaPointerGetAttributes(&pa, device_rgba8) != cudaSuccess ||
+        (pa.type != cudaMemoryTypeDevice && pa.type != cudaMemoryTypeManaged)) {
+        (void) cudaGetLastError();
+        return fail(RT_B200_ERR_ARG, "device_rgba8 is not a device pointer");
+    }
+    if (pa.type == cudaMemoryTypeDevice && pa.device != device)
+        return fail(RT_B200_ERR_ARG, "device_rgba8 lives on device %d, the frame is rendered on device %d", pa.device, device);
+
+    std::lock_guard<std::mutex> lock(g_no_alloc_mutex);
+    unsigned char *d_scratch = nullptr;
+    int rc = no_alloc_device_scratch(device, &d_scratch);
+    if (rc != RT_B200_OK) return rc;
+
+    // ---- classify and repack into the host image (same rules as rt_b200_upload_scene) ----------------------------
+    unsigned char *H = g_no_alloc_host;
+    std::memset(H, 0, L.total);                       // tile counters = 0; no stale bytes of the previous call
+    double4 *plane = reinterpret_cast<double4 *>(H + L.plane), *sphere = reinterpret_cast<double4 *>(H + L.sphere);
+    float4 *sphere_f = reinterpret_cast<float4 *>(H + L.sphere_f);
+    double *quadric = reinterpret_cast<double *>(H + L.quadric), *cubic = reinterpret_cast<double *>(H + L.cubic);
+    unsigned *cubic_mask = reinterpret_cast<unsigned *>(H + L.cubic_mask);
+    int *orig = reinterpret_cast<int *>(H + L.orig);
+    double *coef_full = reinterpret_cast<double *>(H + L.coef_full);
+    float4 *material = reinterpret_cast<float4 *>(H + L.material), *material_pi = reinterpret_cast<float4 *>(H + L.material_pi);
+    rt::LightDev *ldev = reinterpret_cast<rt::LightDev *>(H + L.lights);
+    size_t filled[4] = {0, 0, 0, 0};
+    size_t class_base[4] = {0, L.n_class[0], L.n_class[0] + L.n_class[1], L.n_class[0] + L.n_class[1] + L.n_class[2]};
+    float center_max = 0.0f, r2_max = 0.0f;
+    bool cull_safe = true;
+    const char *obj_bytes = static_cast<const char *>(objects);
+    for (size_t i = 0; i < n_objects; i++) {
+        double k[20];
+        float refl, color[3];
+        std::memcpy(k, obj_bytes + RT_B200_OBJECT_BYTES * i, 160);
+        std::memcpy(&refl, obj_bytes + RT_B200_OBJECT_BYTES * i + 160, 4);
+        std::memcpy(color, obj_bytes + RT_B200_OBJECT_BYTES * i + 164, 12);
+        std::memcpy(coef_full + 20 * i, k, 160);
+        const float pi_f = 3.14159274101257324f;
+        material[i] = make_float4(refl, color[0], color[1], color[2]);
+        material_pi[i] = make_float4(refl, color[0] / pi_f, color[1] / pi_f, color[2] / pi_f);
+        if (!(fabsf(color[0]) < 1e5f && fabsf(color[1]) < 1e5f && fabsf(color[2]) < 1e5f)) cull_safe = false;
+        const rt::ObjClass cls = classify(k);
+        const size_t j = filled[cls]++;
+        orig[class_base[cls] + j] = (int) i;          // class-sorted slot -> original index (order kept inside a class)
+        switch (cls) {
+            case rt::CLS_PLANE:
+                plane[j] = make_double4(k[rt::LX], k[rt::LY], k[rt::LZ], k[rt::CC]);
+                break;
+            case rt::CLS_SPHERE: {
+                sphere[j] = make_double4(k[rt::LX], k[rt::LY], k[rt::LZ], k[rt::CC]);
+                const double cx = -0.5 * k[rt::LX], cy = -0.5 * k[rt::LY], cz = -0.5 * k[rt::LZ];
+                const double r2 = cx * cx + cy * cy + cz * cz - k[rt::CC];
+                sphere_f[j] = make_float4((float) cx, (float) cy, (float) cz, (float) r2);
+                r2_max = fmaxf(r2_max, nextafterf((float) fabs(r2), INFINITY));
+                center_max = fmaxf(center_max, fmaxf(fabsf((float) cx), fmaxf(fabsf((float) cy), fabsf((float) cz))));
+                break;
+            }
+            case rt::CLS_QUADRIC:
+                for (int q = rt::X2; q <= rt::CC; q++) quadric[10 * j + (q - rt::X2)] = k[q];
+                break;
+            case rt::CLS_CUBIC: {
+                unsigned mask = 0;
+                for (int q = 0; q < 20; q++) {
+                    cubic[20 * j + q] = k[q];
+                    if (k[q] != 0.0) mask |= 1u << q;
+                }
+                cubic_mask[j] = mask;
+                break;
+            }
+        }
+    }
+    const char *light_bytes = static_cast<const char *>(lights);
+    for (size_t j = 0; j < n_lights; j++) {
+        const char *rec = light_bytes + RT_B200_LIGHT_BYTES * j;
+        double p[3];
+        float col[3];
+        std::memcpy(p, rec + 8, 24);
+        std::memcpy(col, rec + 32, 12);
+        ldev[j] = rt::LightDev{p[0], p[1], p[2], col[0], col[1], col[2], rec[0] != 0 ? 1 : 0};
+        if (!(fabsf(col[0]) < 1e15f && fabsf(col[1]) < 1e15f && fabsf(col[2]) < 1e15f)) cull_safe = false;
+    }
+
+    // ---- scene view and frame parameters over the DEVICE copy of the image -----------------------------------------
+    rt::SceneView v{};                                 // grid.cell_start == nullptr: brute force
+    v.n_plane = (int) L.n_class[rt::CLS_PLANE];
+    v.n_sphere = (int) L.n_class[rt::CLS_SPHERE];
+    v.n_quadric = (int) L.n_class[rt::CLS_QUADRIC];
+    v.n_cubic = (int) L.n_class[rt::CLS_CUBIC];
+    v.n_objects = (int) n_objects;
+    v.n_lights = (int) n_lights;
+    v.plane = reinterpret_cast<const double4 *>(d_scratch + L.plane);
+    v.sphere = reinterpret_cast<const double4 *>(d_scratch + L.sphere);
+    v.sphere_f = reinterpret_cast<const float4 *>(d_scratch + L.sphere_f);
+    v.quadric = reinterpret_cast<const double *>(d_scratch + L.quadric);
+    v.cubic = reinterpret_cast<const double *>(d_scratch + L.cubic);
+    v.orig_index = reinterpret_cast<const int *>(d_scratch + L.orig);
+    v.coef_full = reinterpret_cast<const double *>(d_scratch + L.coef_full);
+    v.material = reinterpret_cast<const float4 *>(d_scratch + L.material);
+    v.material_pi = reinterpret_cast<const float4 *>(d_scratch + L.material_pi);
+    v.lights = reinterpret_cast<const rt::LightDev *>(d_scratch + L.lights);
+    v.sphere_center_max = center_max;
+
+    rt::FrameParams f;
+    std::memcpy(f.m, camera_matrix, sizeof(f.m));
+    for (int r = 0; r < 3; r++)   // origin = M * (0,0,0,1) in GLM's association, update-cpu.cpp:123
+        f.origin[r] = (f.m[r] * 0.0 + f.m[4 + r] * 0.0) + (f.m[8 + r] * 0.0 + f.m[12 + r] * 1.0);
+    f.aspect = (double) px_width / px_height;
+    f.tan_half_fov = std::tan(0.5 * vertical_fov_rad);
+    std::memcpy(f.bg, bg_color, sizeof(f.bg));
+    f.max_reflections = (int) max_reflections;
+    f.width = (int) px_width;
+    f.height = (int) px_height;
+    f.strip_rows = (int) px_height;
+    f.rank = 0;
+    f.world = 1;
+    f.local_rows = (int) px_height;
+    f.row0 = 0;
+    f.rows = (int) px_height;
+    f.direct = 0;
+    f.out = static_cast<uchar4 *>(device_rgba8);
+    f.counters = nullptr;
+
+    cudaStream_t stream = nullptr;   // legacy default stream: nothing to create
+    CUDA_TRY(cudaMemcpyAsync(d_scratch, H, L.total, cudaMemcpyHostToDevice, stream));
+    CUDA_TRY(cudaStreamSynchronize(stream));          // the staging area is pageable: done with it before the clock starts
+    const double t0 = now_seconds();
+    if (rt::wave_scene_fits(v)) {
+        const rt::WaveLaunch wl{reinterpret_cast<unsigned long long *>(d_scratch + L.tile_counter),
+                                reinterpret_cast<const unsigned *>(d_scratch + L.cubic_mask), r2_max, -1, 0, 1, cull_safe ? 1 : 0, 0,
+                                nullptr, nullptr, nullptr, 0u, 0, 1, nullptr, nullptr, 0, 0, 0, 0};
+        const cudaError_t e = rt::launch_render_wave(v, f, wl, stream);
+        if (e != cudaSuccess) return fail(RT_B200_ERR_CUDA, "launch_render_wave: %s", cudaGetErrorString(e));
+    }
+    else {
+        CUDA_TRY(rt::launch_render_exact(v, f, stream));
+    }
+    CUDA_TRY(cudaStreamSynchronize(stream));
+    if (elapsed_ms) *elapsed_ms = (float) ((now_seconds() - t0) * 1e3);
+    return RT_B200_OK;
+}
+
+} // extern "C"

@@ -212,6 +212,38 @@ int rt_b200_get_grid_info(rt_b200_ctx *ctx, uint32_t out[6]);
 int rt_b200_strip_layout(uint32_t px_height, uint32_t strip_rows, int rank, int world_size, int32_t *image_rows,
                          size_t capacity, uint32_t *local_rows);
 
+/* ---- one frame without any allocation -------------------------------------------------------------------------------
+ * No counterpart in the reference; added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * Renders ONE frame of a scene given in the reference's layouts (the same arguments as rt_b200_upload_scene, plus the
+ * camera matrix of rt_b200_update) into a DEVICE buffer the caller owns — no context, no rt_b200_upload_scene.  The
+ * wavefront kernel's device scratch — its tile counters and the class-sorted copy of the scene it reads, which
+ * rt_b200_upload_scene would cudaMalloc — lives in one file-scope `static __device__ __align__(256)` array of
+ * RT_B200_NO_ALLOC_SCRATCH_BYTES (1 MiB) inside the library; every GPU that loads the library holds that array until the
+ * process exits.  The call makes no cudaMalloc / cudaFree / cudaHostAlloc, creates no stream or event, and calls no
+ * allocating library routine: one host-to-device copy of the repacked scene (from a static host staging area), one kernel
+ * launch on the legacy default stream, one stream synchronise.
+ *   device_rgba8 : device pointer on `device`, 16-byte aligned, device_bytes >= px_width * px_height * 4; receives the
+ *                  frame exactly as rt_b200_update + rt_b200_gather deliver it (RGBA8, row 0 = bottom, alpha 255)
+ *   *elapsed_ms  : (may be NULL) host clock around launch -> kernel complete (no events are created)
+ * Limits (RT_B200_ERR_ARG with a message naming the sizes): the repacked scene must fit the scratch array — about 250
+ * bytes per sphere or plane, 280 per quadric, 360 per cubic, 40 per light: the synthetic 4096 + 64 + 16 scene of
+ * BASELINE.json needs 1 024 000 bytes and fits, 6 000 spheres do not; rt_b200_no_alloc_scratch_needed tells exactly.  Scenes
+ * whose lights / quadrics / cubics exceed the kernel's shared memory render through the exact per-pixel kernel, as in
+ * rt_b200_update.  The sphere grid (option "accel") is not available here: brute force, like the reference.
+ * Sharing: every call uses the same array (and the same host staging area), which keeps the previous call's contents;
+ * each call rewrites everything it reads, including the tile counters that must start at zero.  Calls are serialised by
+ * a mutex and are synchronous, so calls through this entry point never overlap on the GPU; anything ELSE that touched the
+ * array concurrently would race — there is nothing else: the array is private to this entry point. */
+#define RT_B200_NO_ALLOC_SCRATCH_BYTES 1048576
+int rt_b200_render_no_alloc(uint32_t px_width, uint32_t px_height, double vertical_fov_rad, const float bg_color[3],
+                            uint32_t max_reflections, const void *objects, size_t n_objects, const void *lights,
+                            size_t n_lights, const double camera_matrix[16], int device, void *device_rgba8,
+                            size_t device_bytes, float *elapsed_ms);
+/* Host-only helper (needs no GPU): scratch bytes rt_b200_render_no_alloc needs for a scene with these objects / lights. */
+int rt_b200_no_alloc_scratch_needed(const void *objects, size_t n_objects, size_t n_lights, size_t *bytes);
+
 /* Library build tag, e.g. "rt_b200 0.1 sm_100a". */
 const char *rt_b200_version(void);
 
