@@ -78,15 +78,17 @@ struct WaveHits {
 
 struct WaveCtl {
     int pool_count;
-    int n_hits;
-    int tile;
-    int warp_base[MAX_WARPS];
+    int n_hits[2];               // hits of the current wave ([wave & 1]); the other word is zeroed for the next wave
+    int next_tile[2];            // this CTA's next tile (n_tiles = none left), double-buffered: while a wave traces the tile
+                                 // of buffer b, warp 0 pulls the following one into buffer b ^ 1 — with its cam_x / cam_y —
+                                 // so a primary wave starts without a barrier of its own
+    int last_cta;                // epilogue: this CTA was the last one of the launch to finish
     int shadow_cache[LIGHT_CHUNK];
     int occ_found[2];            // occluders found so far by [0] the sphere pass, [1] the cubic pass
     int prim_rays, prim_hits;    // recent primary rays / hits of this CTA (decayed): the cubic filter runs on primary
     int prim_filter;             // rays only while enough of them miss for a proven miss to pay for the filter
     int dyn_slot, dyn_group;     // dynamic ownership: the last slot -> group lookup (thread 0 only)
-    double cam_x[32], cam_y[MAX_WARPS];   // camera-plane coordinates of the current tile's 32 columns / W/32 rows
+    double cam_x[2][32], cam_y[2][MAX_WARPS];   // camera-plane coordinates of the buffered tile's columns / rows
 };
 
 // Frame synchronisation of the fused multi-GPU gather, done by the render kernel itself (no extra launches):

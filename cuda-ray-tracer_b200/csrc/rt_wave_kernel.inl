@@ -30,9 +30,15 @@ __device__ __forceinline__ void store_primary(uchar4 *out, size_t index, bool fi
 // one GPU, the other CTAs of the SM cover the round trip, and a coarser tail on several — and a warp-collective
 // variant that pre-reads the slot table while the atomic is in flight: 2 us per frame better with the dynamic split,
 // 1 % worse without.)
-__device__ __forceinline__ int next_tile_index(const WaveConfig &cfg, WaveCtl &ctl, int n_tiles, int tile_rows)
+// Split in two so that the counter's round trip overlaps a wave of tracing: pull_tile() issues the atomic, resolve_tile()
+// — called after phase A — turns its result into a tile index.
+__device__ __forceinline__ unsigned pull_tile(const WaveConfig &cfg)
 {
-    const unsigned t = atomicAdd(reinterpret_cast<unsigned *>(cfg.tile_counter), 1u);
+    return atomicAdd(reinterpret_cast<unsigned *>(cfg.tile_counter), 1u);
+}
+
+__device__ __forceinline__ int resolve_tile(const WaveConfig &cfg, WaveCtl &ctl, unsigned t, int n_tiles)
+{
     if (cfg.dyn.counters == nullptr) return t < (unsigned) n_tiles ? (int) t : n_tiles;
     const unsigned tiles_per_group = cfg.tiles_per_group;
     const unsigned k = magic_div(t, cfg.inv_tiles_per_group), r = t - k * tiles_per_group;   // t * tiles_per_group < 2^32
@@ -67,6 +73,22 @@ __device__ __forceinline__ int next_tile_index(const WaveConfig &cfg, WaveCtl &c
     RT_CHECK(grp < cfg.dyn.n_groups && (unsigned) grp * tiles_per_group + r < (unsigned) n_tiles);
     // the group's tiles in the frame's tile space: group g covers tile rows [g * h, (g + 1) * h), h = group_rows / tile_rows
     return (int) ((unsigned) grp * tiles_per_group + r);
+}
+
+// Warp 0: publish tile t (n_tiles = none left) in buffer b together with the camera-plane coordinates of its columns and
+// rows — the two divisions of primary ray generation (update-cpu.cpp:84-87), once per column / row of the tile.
+template <int W>
+__device__ __forceinline__ void publish_tile(WaveCtl &ctl, int b, int t, int n_tiles, const FrameParams &f, const WaveConfig &cfg, int lane)
+{
+    if (lane == 0) ctl.next_tile[b] = t;
+    if (t < n_tiles) {
+        const int ty = (int) magic_div((unsigned) t, cfg.inv_tiles_x), tx = t - ty * cfg.tiles_x;
+        if (lane < TileGeom<W>::TILE_W) ctl.cam_x[b][lane] = primary_cam_x(f, tx * TileGeom<W>::TILE_W + lane);
+        if (lane < TileGeom<W>::TILE_ROWS) {
+            const int lrow = f.row0 + ty * TileGeom<W>::TILE_ROWS + lane;
+            ctl.cam_y[b][lane] = primary_cam_y(f, local_to_image_row(lrow, f.strip_rows, f.rank, f.world));
+        }
+    }
 }
 
 __device__ __forceinline__ float blend(float out, float ratio, float c) { return (1.0f - ratio) * out + ratio * c; }
@@ -134,6 +156,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         s.lights = lt;
         if (tid == 0) {
             ctl.pool_count = 0;
+            ctl.n_hits[0] = ctl.n_hits[1] = 0;
             ctl.occ_found[0] = ctl.occ_found[1] = 0;
             ctl.prim_rays = ctl.prim_hits = 0;
             ctl.prim_filter = 1;
@@ -196,50 +219,44 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
     const d3 cam_origin = d3{f.origin[0], f.origin[1], f.origin[2]};
     const int n_tiles = cfg.tiles_x * cfg.tiles_y;
     const bool vec_ok = (f.width & 3) == 0;   // rows start 16-byte aligned (packed and assembled layout alike)
-    bool tiles_left = true;
     unsigned waves = 0;
+    // Barriers per wave: one after the hit list is built, one after the shadow rays (per chunk of 32 lights), one at the
+    // end.  A primary wave needs none of its own: its tile and the tile's camera terms were put into ctl.next_tile /
+    // cam_x / cam_y [par] by warp 0 during an earlier wave (round 1 spent three barriers on picking a tile, publishing it
+    // and publishing the camera terms; `barrier` was 10-18 % of the stall samples).
+    if (warp == 0) {
+        int t = 0;
+        if (lane == 0) t = resolve_tile(cfg, ctl, pull_tile(cfg), n_tiles);
+        t = __shfl_sync(0xffffffffu, t, 0);
+        publish_tile<W>(ctl, 0, t, n_tiles, f, cfg, lane);
+    }
+    __syncthreads();
+    int par = 0;   // the buffer that holds this CTA's next tile (uniform over the CTA)
     for (;;) {
-        if (COUNT && (++waves & 63u) == 0) {   // keep the 32-bit per-thread tallies far from overflow
+        if (COUNT && (waves & 63u) == 63u) {   // keep the 32-bit per-thread tallies far from overflow
             flush_tally(tl, f.counters);
             tl.clear();
         }
-        // ---- choose the next wave: pooled bounce rays when a full wave is waiting (or nothing else is left) ----
-        if (tid == 0) {
-            ctl.tile = -1;
-            if (ctl.pool_count < WAVE && tiles_left) ctl.tile = next_tile_index(cfg, ctl, n_tiles, TILE_ROWS);
-            ctl.n_hits = 0;
-        }
-        __syncthreads();
-        int tile = ctl.tile;
-        const bool prim_filter = ctl.prim_filter != 0;
-        if (tile >= n_tiles) {
-            tiles_left = false;
-            tile = -1;
-        }
+        // ---- choose the wave: pooled bounce rays when a full wave is waiting (or no tile is left), else the next tile ----
+        // (every thread decides for itself from words that are stable since the last barrier)
         const int pooled = ctl.pool_count;
-        if (tile < 0 && pooled == 0) {
-            if (!tiles_left) break;
-            continue;   // unreachable in practice: tile < 0 with tiles_left means pool >= WAVE
-        }
-        if (tile >= 0 && tid < TILE_W + TILE_ROWS) {
-            // the two divisions of primary ray generation (update-cpu.cpp:84-87) once per column / row of the tile
-            const int ty = (int) magic_div((unsigned) tile, cfg.inv_tiles_x), tx = tile - ty * cfg.tiles_x;
-            if (tid < TILE_W) {
-                ctl.cam_x[tid] = primary_cam_x(f, tx * TILE_W + tid);
-            }
-            else {
-                const int lrow = f.row0 + ty * TILE_ROWS + (tid - TILE_W);
-                ctl.cam_y[tid - TILE_W] = primary_cam_y(f, local_to_image_row(lrow, f.strip_rows, f.rank, f.world));
-            }
-        }
-        __syncthreads();   // everyone has read ctl.tile / pool_count before they change
+        const int tile_next = ctl.next_tile[par];
+        const bool prim_filter = ctl.prim_filter != 0;
+        const bool primary = pooled < WAVE && tile_next < n_tiles;
+        if (!primary && pooled == 0) break;
+        const int tile = primary ? tile_next : -1;
+        const int hp = (int) (waves & 1u);
+        if (tid == 0) ctl.n_hits[hp ^ 1] = 0;   // last read before the previous wave's final barrier, next used after this wave's
+        unsigned pulled = 0u;
+        if (primary && tid == 0) pulled = pull_tile(cfg);   // the tile after this one: the result is consumed after phase A
+        const int take = pooled < WAVE ? pooled : WAVE;
+        const int pool_base = pooled - take;                // bounce wave: what stays in the pool
 
         // ---- ray of this thread -----------------------------------------------------------------------
         bool active;
         d3 o, d;
         float out_r = 0.f, out_g = 0.f, out_b = 0.f, ratio = 1.0f;
         int bounces = 0, pixel = 0;
-        const bool primary = tile >= 0;
         if (primary) {
             const int ty = (int) magic_div((unsigned) tile, cfg.inv_tiles_x), tx = tile - ty * cfg.tiles_x;
             const int x = tx * TILE_W + (warp % WX) * 8 + (lane & 7);
@@ -251,16 +268,14 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
             if (in_buf && !active && !f.direct) f.out[pixel] = make_uchar4(0, 0, 0, 0);   // padding row past the image
             if (active) {
                 o = cam_origin;
-                d = primary_dir_cam(f, cam_origin, ctl.cam_x[(warp % WX) * 8 + (lane & 7)], ctl.cam_y[(warp / WX) * 4 + (lane >> 3)]);
+                d = primary_dir_cam(f, cam_origin, ctl.cam_x[par][(warp % WX) * 8 + (lane & 7)], ctl.cam_y[par][(warp / WX) * 4 + (lane >> 3)]);
                 if (COUNT) tl.n[CNT_PRIMARY]++;
             }
         }
         else {
-            const int take = pooled < WAVE ? pooled : WAVE;
-            const int base = pooled - take;
             active = tid < take;
             if (active) {
-                const int r = base + tid;
+                const int r = pool_base + tid;
                 RT_CHECK(r >= 0 && r < 2 * WAVE);
                 o = d3{pool.ox[r], pool.oy[r], pool.oz[r]};
                 d = d3{pool.dx[r], pool.dy[r], pool.dz[r]};
@@ -269,8 +284,6 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
                 pixel = pool.pixel[r];
                 bounces = pool.bounces[r];
             }
-            __syncthreads();
-            if (tid == 0) ctl.pool_count = base;
         }
 
         // ---- phase A + B: nearest hit, hit record, compact hit list ---------------------------------------
@@ -311,18 +324,25 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
             else { out_r = blend(out_r, ratio, f.bg[0]); out_g = blend(out_g, ratio, f.bg[1]); out_b = blend(out_b, ratio, f.bg[2]); }
             final_px = true;
         }
+        if (primary && warp == 0) {
+            // the tile after this one, pulled before phase A: into the other buffer, nobody reads that one during this wave
+            int t = 0;
+            if (lane == 0) t = resolve_tile(cfg, ctl, pulled, n_tiles);
+            t = __shfl_sync(0xffffffffu, t, 0);
+            publish_tile<W>(ctl, par ^ 1, t, n_tiles, f, cfg, lane);
+        }
         {
+            // hit list: one shared atomic per warp (the order of the list is immaterial: it only spreads the shadow tasks)
             const unsigned m = __ballot_sync(0xffffffffu, hit);
-            if (lane == 0) ctl.warp_base[warp] = __popc(m);
-            __syncthreads();
-            int base = 0;
-            for (int w = 0; w < warp; w++) base += ctl.warp_base[w];
-            RT_CHECK(!hit || base + __popc(m & ((1u << lane) - 1u)) < WAVE);
-            if (hit) wh.hitlist[base + __popc(m & ((1u << lane) - 1u))] = (unsigned short) tid;
-            if (tid == WAVE - 1) ctl.n_hits = base + __popc(m);
+            int wbase = 0;
+            if (lane == 0 && m) wbase = atomicAdd(&ctl.n_hits[hp], __popc(m));
+            wbase = __shfl_sync(0xffffffffu, wbase, 0);
+            RT_CHECK(!hit || wbase + __popc(m & ((1u << lane) - 1u)) < WAVE);
+            if (hit) wh.hitlist[wbase + __popc(m & ((1u << lane) - 1u))] = (unsigned short) tid;
         }
         __syncthreads();
-        const int n_hits = ctl.n_hits;
+        const int n_hits = ctl.n_hits[hp];
+        if (!primary && tid == 0) ctl.pool_count = pool_base;   // everybody has read it; appends follow the next barrier
         if (CUBIC && primary && tid == 0 && g.n_cubic > 0) {
             // the filter costs about a third of an exact test and saves one only for (ray, cubic) pairs that cannot give
             // the nearest hit: a ray has one nearest hit, so with several cubics most pairs are of that kind
@@ -412,6 +432,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
             }
             if (l0 + LIGHT_CHUNK < g.n_lights) __syncthreads();   // the next chunk reuses the occlusion words
         }
+        if (g.n_lights == 0) __syncthreads();   // no shadow phase: the pool bookkeeping above still has to precede the appends below
 
         // ---- phase D (part 2): clamp, blend, bounce ---------------------------------------------------------------
         bool spawn = false;
@@ -463,6 +484,8 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
         if (primary) store_primary(f.out, (size_t) pixel, final_px, px, vec_ok);
         else if (final_px) f.out[pixel] = px;
         __syncthreads();
+        if (primary) par ^= 1;   // the buffer filled during this wave holds the next tile
+        waves++;
     }
     if (COUNT) flush_tally(tl, f.counters);
 
@@ -480,12 +503,12 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
                 asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(cfg.sync.flags + cfg.sync.rank), "r"(cfg.sync.seq) : "memory");
             }
         }
-        ctl.tile = last ? 1 : 0;
+        ctl.last_cta = last ? 1 : 0;
     }
     if (cfg.dyn.counters != nullptr) {
         // the last CTA re-arms this GPU's slot table for the next launch (every other CTA is done with it)
         __syncthreads();
-        if (ctl.tile) {
+        if (ctl.last_cta) {
             for (int k = tid; k < cfg.dyn.max_slots; k += WAVE) {
                 int grp = -1;
                 if (k < cfg.dyn.ahead) {
@@ -498,7 +521,7 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
     }
     if (cfg.sync.go != nullptr && cfg.sync.rank == 0) {
         __syncthreads();
-        if (ctl.tile && tid < cfg.sync.world) {   // rank 0 consumes the frame: wait for every rank's flag
+        if (ctl.last_cta && tid < cfg.sync.world) {   // rank 0 consumes the frame: wait for every rank's flag
             const long long t0 = clock64();
             for (;;) {
                 unsigned v;
