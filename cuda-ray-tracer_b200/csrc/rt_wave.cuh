@@ -136,6 +136,7 @@ struct WaveConfig {
     int use_cubic_filter;
     int use_grid;                // sphere class through the uniform grid (rt_grid.cuh) instead of the brute-force loop
     int cull_backfacing;         // skip shadow rays of lights whose Lambert factor is 0 at the hit (they add exactly 0)
+    int lone_kernel;             // host side: use the lone-cubic instantiation for scenes of exactly one cubic object
     unsigned long long *tile_counter;   // [0] next tile, [1] CTAs finished; the last CTA leaves both at 0
     WaveSync sync;
     WaveDyn dyn;

@@ -95,11 +95,23 @@ __device__ __forceinline__ float blend(float out, float ratio, float c) { return
 
 } // namespace
 
-template <int W, int MINB, bool COUNT, bool CUBIC, bool GRID>
+// LONE: the scene is exactly one cubic-class object (four of the eight bundled scenes).  The class counts become
+// compile-time constants, so the plane / sphere / quadric code and the class loops disappear from that instantiation:
+// round 2's ncu captures showed only ~3 700 of the generic kernel's 11 800 instructions executing on such a scene, but
+// scattered over its whole 185 KB, with 10-20 % of the stall samples waiting for instruction fetch at the far jumps.
+template <int W, int MINB, bool COUNT, bool CUBIC, bool GRID, bool LONE = false>
 __global__ void __launch_bounds__(W, MINB)
-render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ FrameParams f,
+render_wave_kernel(const __grid_constant__ SceneView g_param, const __grid_constant__ FrameParams f,
                    const __grid_constant__ WaveConfig cfg)
 {
+    SceneView g_lone;
+    if (LONE) {
+        g_lone = g_param;
+        g_lone.n_plane = g_lone.n_sphere = g_lone.n_quadric = 0;
+        g_lone.n_cubic = 1;
+        g_lone.n_objects = 1;
+    }
+    const SceneView &g = LONE ? g_lone : g_param;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int WAVE = W;
     constexpr int WX = TileGeom<W>::WX;              // warps side by side in a tile, an 8x4 sub-tile per warp
@@ -539,20 +551,20 @@ render_wave_kernel(const __grid_constant__ SceneView g, const __grid_constant__ 
 
 namespace {
 
-template <int W, int MINB, bool CUBIC, bool GRID = false>
+template <int W, int MINB, bool CUBIC, bool GRID = false, bool LONE = false>
 cudaError_t launch_wave_variant(const SceneView &scene, const FrameParams &frame, WaveConfig cfg, size_t scene_smem,
                                 int n_sm, int max_smem, cudaStream_t stream)
 {
     static std::atomic<unsigned long long> attr_set{0ULL};   // bit d: the attribute is set on device d (it is per device)
-    auto kern = frame.counters ? render_wave_kernel<W, MINB, true, CUBIC, GRID> : render_wave_kernel<W, MINB, false, CUBIC, GRID>;
+    auto kern = frame.counters ? render_wave_kernel<W, MINB, true, CUBIC, GRID, LONE> : render_wave_kernel<W, MINB, false, CUBIC, GRID, LONE>;
     cudaError_t e;
     int dev = 0;
     e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
     // Setting it twice from two threads is harmless; devices past 63 set it on every launch.
     if (dev >= 64 || !((attr_set.load(std::memory_order_acquire) >> dev) & 1ULL)) {
-        e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, true, CUBIC, GRID>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, false, CUBIC, GRID>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, true, CUBIC, GRID, LONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(render_wave_kernel<W, MINB, false, CUBIC, GRID, LONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
         if (e != cudaSuccess) return e;
         if (dev < 64) attr_set.fetch_or(1ULL << dev, std::memory_order_release);
     }
@@ -634,6 +646,7 @@ cudaError_t launch_render_wave_t(const SceneView &scene, const FrameParams &fram
     cfg.use_shadow_cache = wl.shadow_cache >= 0 ? wl.shadow_cache : (scene.n_objects >= 8 ? 1 : 0);
     cfg.use_cubic_filter = wl.cubic_filter;
     cfg.cull_backfacing = wl.cull_backfacing;
+    cfg.lone_kernel = wl.lone_kernel;
     // with the grid the FP32 sphere array is read a few candidates at a time (L1/L2): it is not staged, which leaves
     // room for three CTAs per SM; rays the walker refuses (rt_grid.cuh: grid_ray_ok) run the brute-force loop from L2
     cfg.use_grid = (wl.accel && scene.grid.cell_start != nullptr && scene.n_sphere > 0) ? 1 : 0;
@@ -652,6 +665,10 @@ cudaError_t launch_render_wave_t(const SceneView &scene, const FrameParams &fram
                      : launch_wave_grid_plain(scene, frame, cfg, scene_smem, n_sm, max_smem, wl.variant, stream);
     int variant = wl.variant;
     if (variant <= 0) variant = (3 * cta256 <= (size_t) sm_smem) ? 3 : 5;
+    if (CUBIC && cfg.lone_kernel && scene.n_objects == 1 && scene.n_cubic == 1) {   // the lone-cubic instantiations
+        if (variant == 3) return launch_wave_variant<256, 3, CUBIC, false, CUBIC>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
+        if (variant == 2) return launch_wave_variant<256, 2, CUBIC, false, CUBIC>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
+    }
     switch (variant) {
 #define RT_WAVE_CASE(CODE, THREADS, MINB) \
         case CODE: return launch_wave_variant<THREADS, MINB, CUBIC>(scene, frame, cfg, scene_smem, n_sm, max_smem, stream);
