@@ -57,14 +57,34 @@ def load_peaks() -> dict:
     return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0, "_source": "fallback"}
 
 
-def measured_traffic():
-    """dram__bytes_read + dram__bytes_write per launch of the render kernel, from the committed ncu capture."""
-    path = os.path.join(ROOT, "profiles", "r1_traffic.json")
-    try:
-        with open(path) as f:
-            return int(json.load(f)["dram_bytes_per_launch"])
-    except (OSError, KeyError, ValueError):
-        return None
+def ncu_summaries(labels):
+    """Pipe utilisation and DRAM traffic of the render kernel per scene, from the committed ncu --set full summaries
+    (profiles/r2_final_wave_<scene>.txt, written by tools/ncu_summary.py from captures of this code)."""
+    import re
+    out = {}
+    for label in labels:
+        path = os.path.join(ROOT, "profiles", "r2_final_wave_{}.txt".format(label))
+        try:
+            t = open(path).read()
+        except OSError:
+            continue
+
+        def g(key):
+            m = re.search(re.escape(key) + r"\s+([0-9.]+)\s*(\w*)", t)
+            return (float(m.group(1)), m.group(2)) if m else (None, "")
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        rd, ru = g("dram__bytes_read.sum")
+        wr, wu = g("dram__bytes_write.sum")
+        dur, du = g("gpu__time_duration.sum")
+        out[label] = {
+            "fma_pipe_pct": g("sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active")[0],
+            "fp64_pipe_pct": g("sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active")[0],
+            "issue_active_pct": g("smsp__issue_active.avg.pct_of_peak_sustained_active")[0],
+            "lanes_per_instruction": g("smsp__thread_inst_executed_per_inst_executed.ratio")[0],
+            "dram_bytes": (rd * scale.get(ru, 1.0) + wr * scale.get(wu, 1.0)) if rd is not None and wr is not None else None,
+            "ncu_ms": dur * (1.0 if du == "ms" else 1e-3) if dur is not None else None,
+        }
+    return out
 
 
 def fp32_peak_tflops(n_sms: int, sm_mhz: float) -> float:
@@ -371,6 +391,16 @@ def run_b200(args):
                 "fb_write_gbs": sc.px_width * sc.px_height * 4 / rms / 1e6,
             }
         achieved = flops_step / render_ms_sum / 1e9 / world    # TFLOP/s per GPU over the render kernels
+        grid_mode = args.accel != 0 and any(len(sc.objects) >= 64 for _, sc, _ in renderers)
+        ncu_labels = [label if args.workload == "bundled4k" else ("synthetic_a1" if grid_mode else "synthetic_a0") for label, _, _ in renderers]
+        ncu = ncu_summaries(ncu_labels)
+        weights = {nl: float(kern[i, 0]) for i, nl in enumerate(ncu_labels)}
+
+        def ncu_w(key):
+            have = [(ncu[k][key], weights[k]) for k in ncu if ncu[k].get(key) is not None]
+            return sum(v * w for v, w in have) / sum(w for _, w in have) if have else None
+        tr = [ncu[k]["dram_bytes"] for k in ncu if ncu[k].get("dram_bytes") is not None]
+        traffic = int(sum(tr) / len(tr)) if tr else None     # dram read + write per launch, mean over the captured frames
         # the same flops split by the pipe that executes them here: sphere tests run through the FP32 filter, every
         # other class (and hit / shading geometry) is FP64 in the reference's operation order, at half the FP32 rate
         fl32 = float(totals["tests_sphere"] * FLOPS["tests_sphere"] + totals["lit"] * FLOPS["lit"])
@@ -405,8 +435,15 @@ def run_b200(args):
                     "d2h_bytes_per_step": int(sum(sc.px_width * sc.px_height * 4 for _, sc, _ in renderers))},
             "gpu_launches": launches,
             "clocks": clocks,
-            "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s",
-                         "frac": achieved / fp32_peak, "traffic": measured_traffic(),
+            "roofline": {"bound": "fp32", "achieved": achieved if not grid_mode else None, "peak": fp32_peak, "unit": "TFLOP/s",
+                         "frac": achieved / fp32_peak if not grid_mode else None, "traffic": traffic,
+                         "reference_equivalent_rate": {"tflops": achieved, "of_fp32_peak": achieved / fp32_peak,
+                                                       "what": "canonical flops of the reference's brute-force loops / kernel time: a work rate, "
+                                                               "not a pipe utilisation — with the sphere grid the kernel skips most of that work"} if grid_mode else None,
+                         "ncu_fma_pipe_pct": ncu_w("fma_pipe_pct"), "ncu_fp64_pipe_pct": ncu_w("fp64_pipe_pct"),
+                         "ncu_issue_active_pct": ncu_w("issue_active_pct"), "ncu_lanes_per_instruction": ncu_w("lanes_per_instruction"),
+                         "ncu_per_scene": ncu, "ncu_what": "sm__inst_executed_pipe_{fma,fp64}, smsp__issue_active (% of peak sustained active) from the committed "
+                                                           "captures profiles/r2_final_wave_*.txt, averaged over the step weighted by each frame's kernel time",
                          "peak_source": "148 SMs x 128 lanes x 2 x sm_max_mhz of MEASURED_PEAKS.json ({})".format(peaks["_source"]),
                          "algorithmic_gflop_per_step": flops_step / 1e9, "kernel_ms_per_step": render_ms_sum,
                          "blended": {"frac": t_min_ms / render_ms_sum, "fp32_gflop": fl32 / 1e9, "fp64_gflop": fl64 / 1e9,
