@@ -193,7 +193,7 @@ __device__ __forceinline__ double intersect_slot(const SceneView &g, const Scene
         tl.n[CNT_T_QUADRIC]++;
         return intersect_quadric(s.quadric + 10 * slot, o, d);
     }
-    return -1.0;   // cubic slots are never cached (phase C): one copy less of the exact cubic test in the kernel
+    return -1.0;   // cached cubic slots are not probed here: they become the first cubic of the class search (occluder_cubics)
 }
 
 // ---- phase C: any occluder with EPS < t < max_t (update-cpu.cpp:66-72); returns the occluding slot or -1 ----
@@ -249,8 +249,10 @@ __device__ __forceinline__ int occluder_spheres(const SceneView &g, const SceneS
 // the keys of the filter caches (SceneSmem::hit_o, light_d) that exist when the scene has exactly one cubic: the origin
 // half of the FP32 expansion per hit, the direction half per directional light (a point light's direction differs per
 // hit).  One verdict call site and one exact test for both the cached and the generic form.
+// first: the cubic to test first (the per-light shadow cache's last occluder when that was a cubic), the others follow
+// cyclically — the cached occluder costs no code of its own.
 __device__ __forceinline__ int occluder_cubics(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg, const d3 &o,
-                                               const d3 &d, double max_t, bool segment01, int hit_slot, int light, Tally &tl)
+                                               const d3 &d, double max_t, bool segment01, int hit_slot, int light, int first, Tally &tl)
 {
     const int base = g.n_plane + g.n_sphere + g.n_quadric;
     const float hi = segment01 ? 1.0f : (float) RT_MAX_T;   // = max_t, exact in FP32
@@ -258,7 +260,9 @@ __device__ __forceinline__ int occluder_cubics(const SceneView &g, const SceneSm
     const float dfx = (float) d.x, dfy = (float) d.y, dfz = (float) d.z;
     const bool cached = s.hit_o != nullptr;
 #pragma unroll 1
-    for (int i = 0; i < g.n_cubic; i++) {
+    for (int n = 0; n < g.n_cubic; n++) {
+        int i = n + first;
+        if (i >= g.n_cubic) i -= g.n_cubic;
         tl.n[CNT_T_CUBIC]++;
         if (cfg.use_cubic_filter) {
             const float *kf = s.cubic_f + RT_CF_FLOATS * i;
@@ -276,7 +280,8 @@ __device__ __forceinline__ int occluder_cubics(const SceneView &g, const SceneSm
 
 template <bool CUBIC, bool GRID>
 __device__ __forceinline__ int occluder_wave(const SceneView &g, const SceneSmem &s, const WaveConfig &cfg, WaveCtl &ctl,
-                                             const d3 &o, const d3 &d, double max_t, bool segment01, int hit_slot, int light, Tally &tl)
+                                             const d3 &o, const d3 &d, double max_t, bool segment01, int hit_slot, int light,
+                                             int cached_cubic, Tally &tl)
 {
     for (int i = 0; i < g.n_plane; i++) {
         tl.n[CNT_T_PLANE]++;
@@ -295,19 +300,29 @@ __device__ __forceinline__ int occluder_wave(const SceneView &g, const SceneSmem
         const volatile int *found = ctl.occ_found;
         const long long sphere_pass = (GRID && cfg.use_grid) ? 2000LL : 16LL * g.n_sphere;
         cubic_first = (long long) found[1] * sphere_pass > (long long) found[0] * (600LL * g.n_cubic);
+        if (cached_cubic >= 0) cubic_first = true;   // this light's last occluder was a cubic: try it before anything else
     }
-#pragma unroll 1
-    for (int pass = 0; pass < 2; pass++) {
-        const bool cubics_now = (pass == 0) == cubic_first;
-        int by = -1;
-        if (cubics_now) {
-            if (have_c) by = occluder_cubics(g, s, cfg, o, d, max_t, segment01, hit_slot, light, tl);
-        }
-        else if (have_s) {
-            by = occluder_spheres<GRID>(g, s, cfg, o, d, max_t, segment01, tl);
-        }
+    // straight-line: the sphere search (small code, the hot loop of sphere-heavy scenes) is instantiated twice, the cubic
+    // search (large code) once.  (Both inside one two-pass loop cost the sphere loop its unrolling: C5 brute force +45 %.)
+    const bool both = have_s && have_c;
+    if (have_s && !cubic_first) {
+        const int by = occluder_spheres<GRID>(g, s, cfg, o, d, max_t, segment01, tl);
         if (by >= 0) {
-            if (have_s && have_c) atomicAdd(&ctl.occ_found[cubics_now ? 1 : 0], 1);
+            if (both) atomicAdd(&ctl.occ_found[0], 1);
+            return by;
+        }
+    }
+    if (have_c) {
+        const int by = occluder_cubics(g, s, cfg, o, d, max_t, segment01, hit_slot, light, cached_cubic > 0 ? cached_cubic : 0, tl);
+        if (by >= 0) {
+            if (both) atomicAdd(&ctl.occ_found[1], 1);
+            return by;
+        }
+    }
+    if (have_s && cubic_first) {
+        const int by = occluder_spheres<GRID>(g, s, cfg, o, d, max_t, segment01, tl);
+        if (by >= 0) {
+            if (both) atomicAdd(&ctl.occ_found[0], 1);
             return by;
         }
     }

@@ -412,15 +412,19 @@ render_wave_kernel(const __grid_constant__ SceneView g_param, const __grid_const
                         occ = blocks(intersect_cubic_masked(s.cubic, s.cubic_mask[0], so, sd), max_t);
                     }
                     else {
+                        // per-light shadow cache: the slot that occluded this light last.  A plane / sphere / quadric is
+                        // probed on its own; a cubic becomes the first cubic of the class search
+                        int cached_cubic = -1;
                         if (cfg.use_shadow_cache) {
                             const int cs = ctl.shadow_cache[j];
-                            if (cs >= 0) occ = blocks(intersect_slot(g, s, cs, so, sd, tl), max_t);
+                            const int n_other = g.n_plane + g.n_sphere + g.n_quadric;
+                            if (cs >= n_other) cached_cubic = cs - n_other;
+                            else if (cs >= 0) occ = blocks(intersect_slot(g, s, cs, so, sd, tl), max_t);
                         }
                         if (!occ) {
-                            const int by = occluder_wave<CUBIC, GRID>(g, s, cfg, ctl, so, sd, max_t, l.is_spherical != 0, k, l0 + j, tl);
+                            const int by = occluder_wave<CUBIC, GRID>(g, s, cfg, ctl, so, sd, max_t, l.is_spherical != 0, k, l0 + j, cached_cubic, tl);
                             occ = by >= 0;
-                            // benign race: any occluder will do; cubic slots are not cached (intersect_slot does not probe them)
-                            if (occ && cfg.use_shadow_cache && by < g.n_plane + g.n_sphere + g.n_quadric) ctl.shadow_cache[j] = by;
+                            if (occ && cfg.use_shadow_cache) ctl.shadow_cache[j] = by;   // benign race: any occluder will do
                         }
                     }
                 }

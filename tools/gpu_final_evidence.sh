@@ -17,6 +17,9 @@ for sc in 20spheres quadratic cubic cayley clebsch dingdong monkey_saddle reflec
   python tools/ncu_summary.py $O/ncu_$sc.ncu-rep profiles/r2_final_wave_$sc.txt > /dev/null 2>&1 && cp profiles/r2_final_wave_$sc.txt $O/
 done
 ls profiles/r2_final_wave_*.txt | wc -l | sed 's/^/summaries written: /' | tee -a $S
+# gpurun returns at most 64 MiB: keep three reports (per-line attribution here), drop the others
+for sc in quadratic cubic cayley dingdong monkey_saddle reflection_test synthetic_a1; do rm -f $O/ncu_$sc.ncu-rep; done
+rm -f gpurun_out/final/*.plain.log
 timeout 600 python bench.py > $O/bench.json 2> $O/bench.err; echo "bench exit $?" | tee -a $S
 timeout 400 python bench.py --workload synthetic --steps 3 --warmup 3 --accel 0 > $O/bench_synth_brute.json 2> $O/bench_synth_brute.err; echo "synth brute exit $?" | tee -a $S
 timeout 400 python bench.py --workload synthetic --steps 10 --warmup 3 --accel 1 > $O/bench_synth_grid.json 2> $O/bench_synth_grid.err; echo "synth grid exit $?" | tee -a $S
