@@ -10,8 +10,12 @@ Workload `bundled4k` (default, the configuration the metric is quoted on): one S
 rt_b200_update calls.  `value` = rays cast per second over the whole job (primary + reflection + shadow
 rays), inputs resident on the device.  `e2e` = the same through the C ABI with HOST
 buffers: camera matrix from host memory in, finished RGBA8 frame copied to pinned host memory out, every
-frame.  With N > 1 ranks (one process per GPU) every rank renders its interleaved strips of every frame
-and the strips are all-gathered over NCCL inside rt_b200_update; time is the max over ranks.
+frame.  With N > 1 ranks (one process per GPU) every rank renders its interleaved strips of every frame and
+its render kernel stores the pixels straight into the frame assembled on rank 0 (CUDA IPC over NVLink, flag words
+as the frame barrier; `--gather nccl` selects the NCCL all-gather of packed strips instead); time is the max over
+ranks.  Before anything is timed every frame of the workload is CHECKED (config.frame_check): against the exact
+per-pixel kernel, against the reference CPU build on a pixel sample, and — N > 1 — the assembled frame against a
+1-GPU render; a mismatch ends the run with exit code 3.
 
 `--impl reference` times the reference's own CPU implementation (oracle/_ref = update-cpu.cpp compiled
 unmodified, else the C restatement) on the host cores, on a bounded row sample of the same workload.
