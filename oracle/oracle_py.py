@@ -17,6 +17,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 REF_LIB = os.path.join(HERE, "_ref", "libref_cpu.so")
+REF_FMA_LIB = os.path.join(HERE, "_ref", "libref_cpu_fma.so")   # FMA-contracted build: for the ill-conditioned mask only
 PORT_LIB = os.path.join(HERE, "librt_oracle.so")
 
 IDENTITY = np.eye(4, dtype=np.float64).reshape(16)
@@ -163,16 +164,17 @@ class PortOracle:
 
 class RefCpu:
     """The unmodified reference CPU back-end.  It keeps its state in file-scope globals
-    (update-cpu.cpp:10-19), so exactly one scene is live per process: init() replaces it."""
+    (update-cpu.cpp:10-19), so exactly one scene is live per process (and library): init() replaces it."""
 
     _lib = None
+    LIB_PATH = REF_LIB
 
     @classmethod
     def lib(cls):
         if cls._lib is None:
-            if not os.path.exists(REF_LIB):
-                raise FileNotFoundError(REF_LIB + " (build with `make -C oracle` where /root/reference exists)")
-            L = C.CDLL(REF_LIB)
+            if not os.path.exists(cls.LIB_PATH):
+                raise FileNotFoundError(cls.LIB_PATH + " (build with `make -C oracle` where /root/reference exists)")
+            L = C.CDLL(cls.LIB_PATH)
             L.ref_last_error.restype = C.c_char_p
             L.ref_init.argtypes = [C.c_uint32, C.c_uint32, C.c_double, C.c_void_p, C.c_uint32, C.c_void_p,
                                    C.c_size_t, C.c_void_p, C.c_size_t]
@@ -271,3 +273,55 @@ class RefCpu:
         if rc != 0:
             raise RuntimeError(cls.lib().ref_last_error().decode())
         return out
+
+
+class RefCpuFma(RefCpu):
+    """The same sources compiled with -mfma -ffp-contract=fast.  NOT an oracle: a perturbed run for the mask below."""
+    _lib = None
+    LIB_PATH = REF_FMA_LIB
+
+
+def cpu_has_fma() -> bool:
+    try:
+        with open("/proc/cpuinfo") as f:
+            return " fma " in f.read().replace("\n", " ")
+    except OSError:
+        return False
+
+
+def have_ref_fma() -> bool:
+    return os.path.exists(REF_FMA_LIB) and cpu_has_fma()
+
+
+def _dilate(mask: np.ndarray) -> np.ndarray:
+    """3 x 3 dilation (the mask's 1-pixel safety margin)."""
+    out = mask.copy()
+    h, w = mask.shape
+    for dy in (-1, 0, 1):
+        for dx in (-1, 0, 1):
+            ys, yd = (slice(max(dy, 0), h + min(dy, 0)), slice(max(-dy, 0), h + min(-dy, 0)))
+            xs, xd = (slice(max(dx, 0), w + min(dx, 0)), slice(max(-dx, 0), w + min(-dx, 0)))
+            out[yd, xd] |= mask[ys, xs]
+    return out
+
+
+def ill_conditioned_mask(scene, camera=IDENTITY, threads=1) -> np.ndarray:
+    """bool [H, W]: the pixels where the REFERENCE's own result is ill-conditioned (SURVEY.md §7.1 step 1, §8c acceptance
+    rule "outliers within the mask").  Three runs of the reference CPU back-end on the same frame —
+      A  the oracle build (-O2 -ffp-contract=off)
+      B  the same sources with FMA contraction (-mfma -ffp-contract=fast; skipped on a CPU without FMA)
+      C  build A with every entry of the camera matrix moved up by one ulp
+    — a pixel is in the mask when any two of them differ by more than 1 LSB in some 8-bit channel, plus one pixel of
+    dilation.  Root solving that survives a perturbation of one rounding is well-conditioned; what flips is not."""
+    m = np.ascontiguousarray(camera, dtype=np.float64).reshape(16)
+    runs = [quantize_rgba8(RefCpu(scene).render_rows(m, threads=threads)[0])]
+    if have_ref_fma():
+        runs.append(quantize_rgba8(RefCpuFma(scene).render_rows(m, threads=threads)[0]))
+    m_up = np.nextafter(m, np.where(m >= 0, np.inf, -np.inf))
+    m_up[m == 0.0] = 0.0      # structural zeros of the matrix stay zero
+    runs.append(quantize_rgba8(RefCpu(scene).render_rows(m_up, threads=threads)[0]))
+    mask = np.zeros(runs[0].shape[:2], dtype=bool)
+    for i in range(len(runs)):
+        for j in range(i + 1, len(runs)):
+            mask |= np.abs(runs[i].astype(np.int16) - runs[j].astype(np.int16)).max(axis=-1) > 1
+    return _dilate(mask)

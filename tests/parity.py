@@ -21,8 +21,17 @@ def compare_frames(gpu_rgba: np.ndarray, oracle_rgba: np.ndarray) -> dict:
     }
 
 
-def assert_parity(gpu_rgba, oracle_rgba, what=""):
+def assert_parity(gpu_rgba, oracle_rgba, what="", mask_fn=None):
+    """The acceptance rule.  mask_fn (optional): a callable returning the frame's ill-conditioned-pixel mask, bool [H, W]
+    (oracle_py.ill_conditioned_mask) — called only when some pixel exceeds +-1 LSB, and then every such pixel has to lie
+    inside the mask ("only where the reference's own root solving is ill-conditioned", north_star)."""
     r = compare_frames(gpu_rgba, oracle_rgba)
     assert r["outlier_frac"] <= MAX_OUTLIER_FRAC, "{}: {}".format(what, r)
     assert (gpu_rgba[..., 3] == 255).all(), what + ": alpha"
+    if r["outliers"] and mask_fn is not None:
+        d = np.abs(gpu_rgba.astype(np.int16) - oracle_rgba.astype(np.int16)).max(axis=-1)
+        outside = (d > MAX_LSB) & ~mask_fn()
+        r["outliers_outside_mask"] = int(outside.sum())
+        assert not outside.any(), "{}: {} outlier pixels outside the ill-conditioned mask, e.g. (y, x) = {}".format(
+            what, int(outside.sum()), tuple(int(v) for v in np.argwhere(outside)[0]))
     return r

@@ -132,3 +132,35 @@ def test_quantize_rule(oracle):
     c = np.array([[0.0, 0.5, 1.0], [0.1, 0.998, 0.00196]], dtype=np.float32)
     q = oracle.quantize_rgba8(c)
     assert q.tolist() == [[0, 128, 255, 255], [26, 254, 0, 255]]
+
+
+def test_ill_conditioned_mask(pkg, oracle, scenes_dir):
+    """the mask of pixels where the reference's own result flips under a one-rounding perturbation
+    (FMA contraction, camera matrix + 1 ulp), and the acceptance rule 'outliers only inside the mask' in tests/parity.py."""
+    import numpy as np
+    from cuda_ray_tracer_b200 import camera
+    from parity import assert_parity
+    if not oracle.have_ref():
+        pytest.skip("oracle/_ref/libref_cpu.so not present")
+    load = lambda n: pkg.load_from_file(os.path.join(scenes_dir, n + ".yml")).with_overrides(width=320, height=240)
+    threads = os.cpu_count() or 1
+    # spheres, planes and quadrics are well-conditioned everywhere
+    assert not oracle.ill_conditioned_mask(load("quadratic"), camera.TEST_POSES["identity"], threads).any()
+    assert not oracle.ill_conditioned_mask(load("20spheres"), camera.TEST_POSES["pose_a"], threads).any()
+    # cayley seen from ON the surface (every primary ray has t0 = t1 = 0, delta = 0 analytically): speckle
+    sc = load("cayley")
+    m = camera.TEST_POSES["identity"]
+    mask = oracle.ill_conditioned_mask(sc, m, threads)
+    assert 0 < mask.sum() < 0.02 * mask.size
+    want = oracle.quantize_rgba8(oracle.RefCpu(sc).render_rows(m, threads=threads)[0])
+    ys, xs = np.nonzero(mask)
+    inside = want.copy()
+    inside[ys[:20], xs[:20], :3] ^= 0x40                 # 20 pixels far off, all inside the mask: accepted
+    r = assert_parity(inside, want, "inside", mask_fn=lambda: mask)
+    assert r["outliers"] == 20 and r["outliers_outside_mask"] == 0
+    yo, xo = np.nonzero(~mask)
+    outside = want.copy()
+    outside[yo[0], xo[0], :3] ^= 0x40                    # one pixel outside it: refused
+    with pytest.raises(AssertionError, match="outside the ill-conditioned mask"):
+        assert_parity(outside, want, "outside", mask_fn=lambda: mask)
+    assert_parity(want, want, "exact", mask_fn=lambda: 1 / 0)   # no outliers: the mask is never computed
