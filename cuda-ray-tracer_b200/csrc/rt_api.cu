@@ -398,8 +398,7 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     std::vector<double> quadric, cubic, coef_full(20 * n_objects);
     std::vector<int> orig[4];
     std::vector<unsigned> cubic_mask;
-    float center_max = 0.0f, r2_max = 0.0f, center_norm_max = 0.0f;
-    bool tables_safe = true;   // FP32 tables need |coordinates| < 1e9, r^2 < 1e18 (NaN counts as unsafe)
+    float center_max = 0.0f, r2_max = 0.0f;
     const char *obj_bytes = static_cast<const char *>(objects);
     for (size_t i = 0; i < n_objects; i++) {
         double k[20];
@@ -428,8 +427,6 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
                 c->sphere_r2.push_back(r2);
                 r2_max = fmaxf(r2_max, nextafterf((float) fabs(r2), INFINITY));
                 center_max = fmaxf(center_max, fmaxf(fabsf((float) cx), fmaxf(fabsf((float) cy), fabsf((float) cz))));
-                center_norm_max = fmaxf(center_norm_max, nextafterf((float) sqrt(cx * cx + cy * cy + cz * cz), INFINITY));
-                if (!(fabs(cx) < 1e9 && fabs(cy) < 1e9 && fabs(cz) < 1e9 && fabs(r2) < 1e18)) tables_safe = false;
                 break;
             }
             case rt::CLS_QUADRIC:
@@ -460,7 +457,6 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
         std::memcpy(p, rec + 8, 24);
         std::memcpy(col, rec + 32, 12);
         ldev[j] = rt::LightDev{p[0], p[1], p[2], col[0], col[1], col[2], rec[0] != 0 ? 1 : 0};
-        if (!(fabs(p[0]) < 1e9 && fabs(p[1]) < 1e9 && fabs(p[2]) < 1e9)) tables_safe = false;
         if (!(fabsf(col[0]) < 1e15f && fabsf(col[1]) < 1e15f && fabsf(col[2]) < 1e15f)) c->cull_safe = false;
     }
 
