@@ -30,7 +30,7 @@ EXPORTS = ("rt_b200_upload_scene", "rt_b200_update", "rt_b200_gather", "rt_b200_
            "rt_b200_update_to_host", "rt_b200_frame_export", "rt_b200_frame_attach", "rt_b200_get_launches",
            "rt_b200_host_alloc", "rt_b200_host_free", "rt_b200_host_alloc_shared", "rt_b200_host_free_shared",
            "rt_b200_get_grid_info", "rt_b200_band_layout", "rt_b200_frame_attach_peer",
-           "rt_b200_render_no_alloc", "rt_b200_no_alloc_scratch_needed")
+           "rt_b200_render_no_alloc", "rt_b200_no_alloc_scratch_needed", "rt_b200_debug_timeline")
 
 UNIQUE_ID_BYTES = 128
 IPC_HANDLE_BYTES = 64
@@ -75,6 +75,7 @@ def load_library():
     L.rt_b200_frame_export.argtypes = [vp, vp]
     L.rt_b200_frame_attach.argtypes = [vp, vp]
     L.rt_b200_frame_attach_peer.argtypes = [vp, vp]
+    L.rt_b200_debug_timeline.argtypes = [vp, vp, C.c_size_t, C.POINTER(C.c_uint32)]
     L.rt_b200_render_no_alloc.argtypes = [C.c_uint32, C.c_uint32, C.c_double, vp, C.c_uint32, vp, C.c_size_t, vp, C.c_size_t,
                                           vp, C.c_int, vp, C.c_size_t, C.POINTER(C.c_float)]
     L.rt_b200_no_alloc_scratch_needed.argtypes = [vp, C.c_size_t, C.c_size_t, C.POINTER(C.c_size_t)]
@@ -219,6 +220,13 @@ class Renderer:
     def frame_attach_peer(self, owner: "Renderer"):
         """Same-process fused gather: `owner` is rank 0's Renderer (after frame_export), possibly on another device."""
         _check(load_library().rt_b200_frame_attach_peer(self._h, owner._h))
+
+    def debug_timeline(self) -> np.ndarray:
+        """uint64 [2048, words]: per-CTA stamps of the last launch (timeline build of the library + option "timeline")."""
+        out = np.zeros(2048 * 8, dtype=np.uint64)
+        w = C.c_uint32()
+        _check(load_library().rt_b200_debug_timeline(self._h, _dp(out), out.size, C.byref(w)))
+        return out.reshape(2048, int(w.value))
 
     def launches(self) -> int:
         n = C.c_uint32()

@@ -31,9 +31,9 @@ def _stale() -> bool:
 def build(force: bool = False, verbose: bool = False, checked: bool = False) -> str:
     """checked=True: librt_b200_checked.so with -DRT_B200_CHECKED (index assertions in the kernels, rt_wave.cuh: RT_CHECK)."""
     if checked:
-        out = os.path.join(HERE, "librt_b200_checked.so")
+        out = os.path.join(HERE, "librt_b200_timeline.so" if checked == "timeline" else "librt_b200_checked.so")
         nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-        subprocess.run([nvcc] + NVCC_FLAGS + ["-DRT_B200_CHECKED", "-shared", "-o", out] +
+        subprocess.run([nvcc] + NVCC_FLAGS + ["-DRT_B200_TIMELINE" if checked == "timeline" else "-DRT_B200_CHECKED", "-shared", "-o", out] +
                        [os.path.join(CSRC, s) for s in SOURCES] + ["-ldl"], check=True)
         return out
     if not force and not _stale():
@@ -46,4 +46,4 @@ def build(force: bool = False, verbose: bool = False, checked: bool = False) -> 
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, checked="--checked" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, checked="timeline" if "--timeline" in sys.argv else ("--checked" in sys.argv)))

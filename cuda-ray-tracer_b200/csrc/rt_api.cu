@@ -194,6 +194,7 @@ struct rt_b200_ctx {
     int cubic_filter = 1;
     int cull_backfacing = 1;
     int lone_kernel = 1;             // option: scenes of exactly one cubic object use the kernel specialised for them
+    int timeline = 0;                // option (diagnostic build only): per-CTA time stamps of the last launch, rt_b200_debug_timeline
     // sphere grid (rt_grid.cuh): built at upload; accel = -1 automatic (on from RT_GRID_AUTO_SPHERES
     // sphere-class objects), 0 brute force, 1 on.  Frames are identical either way.
     int accel = -1;
@@ -479,7 +480,8 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
     up(cudaMalloc((void **) &c->d_tile_counter, 2 * RT_MAX_BANDS * sizeof(unsigned long long)), "tile counter");
     if (c->d_tile_counter) up(cudaMemset(c->d_tile_counter, 0, 2 * RT_MAX_BANDS * sizeof(unsigned long long)), "tile counter");
     c->sphere_r2_max = r2_max;
-    up(cudaMalloc((void **) &c->d_counters, sizeof(unsigned long long) * rt::CNT_COUNT), "counters");
+    // work counters, and behind them the per-CTA timeline of the diagnostic build (option "timeline"; 128 KB)
+    up(cudaMalloc((void **) &c->d_counters, sizeof(unsigned long long) * (rt::CNT_COUNT + RT_TL_MAX_CTAS * RT_TL_WORDS)), "counters");
     up(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "stream");
     up(cudaEventCreate(&c->ev_start), "event");
     up(cudaEventCreate(&c->ev_render), "event");
@@ -612,6 +614,8 @@ int render_frame(rt_b200_ctx *c, const double camera_matrix[16], void *host_sink
     f.row0 = 0;
     f.rows = c->local_rows;
     f.counters = c->count ? c->d_counters : nullptr;
+    f.timeline = c->timeline ? c->d_counters + rt::CNT_COUNT : nullptr;
+    if (c->timeline) CUDA_TRY(cudaMemsetAsync(c->d_counters + rt::CNT_COUNT, 0, sizeof(unsigned long long) * RT_TL_MAX_CTAS * RT_TL_WORDS, c->stream));
     // host frame shared by all ranks (rt_b200_host_alloc_shared): every rank copies its own strips to the host
     SharedBlock *blk = (host_sink && c->world > 1) ? find_block(host_sink) : nullptr;
     if (blk && blk->bytes < frame_bytes)
@@ -1176,6 +1180,9 @@ int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
     else if (!std::strcmp(name, "flag_barrier")) {
         c->flag_barrier = value != 0;
     }
+    else if (!std::strcmp(name, "timeline")) {
+        c->timeline = value ? 1 : 0;
+    }
     else if (!std::strcmp(name, "lone_kernel")) {
         c->lone_kernel = value ? 1 : 0;
     }
@@ -1251,6 +1258,16 @@ int rt_b200_get_launches(rt_b200_ctx *c, uint32_t *launches)
     if (c->world > 1 && c->comm && !c->shared_ready) n += 1;                 // strip un-interleave (the all-gather itself is NCCL's)
     if (c->world > 1 && c->shared_ready && c->flag_barrier && !c->sync_in_kernel) n += c->rank == 0 ? 3 : 2;   // sequence-word kernels (kernel 0 only: kernel 1 does the hand-shake itself)
     *launches = n;
+    return RT_B200_OK;
+}
+
+int rt_b200_debug_timeline(rt_b200_ctx *c, uint64_t *out, size_t capacity_words, uint32_t *words_per_cta)
+{
+    if (!c || !out || !words_per_cta) return fail(RT_B200_ERR_ARG, "null argument");
+    *words_per_cta = RT_TL_WORDS;
+    const size_t n = std::min(capacity_words, (size_t) RT_TL_MAX_CTAS * RT_TL_WORDS);
+    CUDA_TRY(cudaSetDevice(c->device));
+    CUDA_TRY(cudaMemcpy(out, c->d_counters + rt::CNT_COUNT, sizeof(uint64_t) * n, cudaMemcpyDeviceToHost));
     return RT_B200_OK;
 }
 
@@ -1513,6 +1530,7 @@ int rt_b200_render_no_alloc(uint32_t px_width, uint32_t px_height, double vertic
     f.direct = 0;
     f.out = static_cast<uchar4 *>(device_rgba8);
     f.counters = nullptr;
+    f.timeline = nullptr;
 
     cudaStream_t stream = nullptr;   // legacy default stream: nothing to create
     CUDA_TRY(cudaMemcpyAsync(d_scratch, H, L.total, cudaMemcpyHostToDevice, stream));

@@ -75,7 +75,12 @@ struct FrameParams {
                            //    are stored at their image position and padding rows are not written
     uchar4 *out;
     unsigned long long *counters;  // [CNT_COUNT] or nullptr
+    unsigned long long *timeline;  // diagnostic build only (-DRT_B200_TIMELINE, option "timeline"): [CTA][RT_TL_WORDS] or nullptr
 };
+
+#define RT_TL_WORDS 8      /* per CTA: global-timer ns at entry, after the prologue, when no tile was left, at loop exit, at kernel
+                              exit; waves run; SM id; tiles rendered */
+#define RT_TL_MAX_CTAS 2048
 
 // local (packed) row -> image row; may be >= height for padding rows
 __host__ __device__ inline int local_to_image_row(int local_row, int strip_rows, int rank, int world)

@@ -192,6 +192,12 @@ int rt_b200_get_timing(rt_b200_ctx *ctx, float out_ms[2]);
  * sequence-word kernels (kernel 1 does that hand-shake inside the render kernel). */
 int rt_b200_get_launches(rt_b200_ctx *ctx, uint32_t *launches);
 
+/* Diagnostic (meaningful only with the timeline build of the library, `build.py --timeline`, and option "timeline" = 1; the
+ * product build leaves zeros): per CTA of the last wavefront-kernel launch *words_per_cta 64-bit words — global-timer ns at kernel
+ * entry, after the prologue, when the CTA first found no tile left, at loop exit, at kernel exit; waves run; SM id; tiles rendered.
+ * tools/gpu_timeline.py prints where the time of a launch goes. */
+int rt_b200_debug_timeline(rt_b200_ctx *ctx, uint64_t *out, size_t capacity_words, uint32_t *words_per_cta);
+
 /* Structural class counts of the uploaded scene: planes, spheres, quadrics, cubics. */
 int rt_b200_get_class_counts(rt_b200_ctx *ctx, uint32_t out[4]);
 
