@@ -76,9 +76,14 @@ int rt_b200_upload_scene(rt_b200_ctx **ctx_out, uint32_t px_width, uint32_t px_h
                          const void *lights, size_t n_lights, int device, int rank, int world_size);
 
 /* == update(camera_matrix), update.h:7.
- * camera_matrix: 16 doubles, GLM column-major (&m[0][0]).  Renders this rank's strips and, when a
- * communicator is attached, all-gathers the strips so that every rank holds the full frame.
- * *elapsed_ms (may be NULL) = CUDA-event time from the first launch to the end of the gather, the value
+ * camera_matrix: 16 doubles, GLM column-major (&m[0][0]).  Renders this rank's strips (world_size 1: the frame) and
+ * assembles the frame inside the call, in one of two ways:
+ *   - a shared frame is attached (rt_b200_frame_attach / _attach_peer, the fused gather below): the render kernel itself
+ *     stores every pixel at its place in the frame on rank 0's GPU; rank 0's call returns when the frame is complete;
+ *   - only a communicator is attached (rt_b200_comm_init): the packed strips are all-gathered over NCCL and un-interleaved,
+ *     so that every rank holds the full frame.
+ * With world_size > 1 and neither, only this rank's rows are rendered (rt_b200_gather exposes them in place).
+ * *elapsed_ms (may be NULL) = CUDA-event time from the first launch to the end of the assembly, the value
  * the reference's update() returns (src/update-cuda.cu:178-189). */
 int rt_b200_update(rt_b200_ctx *ctx, const double camera_matrix[16], float *elapsed_ms);
 
