@@ -194,6 +194,7 @@ struct rt_b200_ctx {
     int cubic_filter = 1;
     int cull_backfacing = 1;
     int lone_kernel = 1;             // option: scenes of exactly one cubic object use the kernel specialised for them
+    int spheres_smem = -1;           // option: -1 automatic, 0 = sphere filter records through L1 instead of shared memory
     int timeline = 0;                // option (diagnostic build only): per-CTA time stamps of the last launch, rt_b200_debug_timeline
     // sphere grid (rt_grid.cuh): built at upload; accel = -1 automatic (on from RT_GRID_AUTO_SPHERES
     // sphere-class objects), 0 brute force, 1 on.  Frames are identical either way.
@@ -543,7 +544,7 @@ rt::WaveLaunch wave_launch_of(const rt_b200_ctx *c, int counter_pair)
     return rt::WaveLaunch{c->d_tile_counter + 2 * counter_pair, c->d_cubic_mask, c->sphere_r2_max, c->shadow_cache, c->wave_variant,
                           c->cubic_filter, (c->cull_backfacing && c->cull_safe) ? 1 : 0,
                           (c->accel > 0 || (c->accel < 0 && c->view.n_sphere >= RT_GRID_AUTO_SPHERES)) ? 1 : 0,
-                          nullptr, nullptr, nullptr, 0u, c->rank, c->world, nullptr, nullptr, 0, 0, 0, 0, c->lone_kernel};
+                          nullptr, nullptr, nullptr, 0u, c->rank, c->world, nullptr, nullptr, 0, 0, 0, 0, c->lone_kernel, c->spheres_smem};
 }
 
 // One render launch of the selected kernel over the packed rows [f.row0, f.row0 + f.rows).
@@ -1179,6 +1180,9 @@ int rt_b200_set_option(rt_b200_ctx *c, const char *name, int64_t value)
     }
     else if (!std::strcmp(name, "flag_barrier")) {
         c->flag_barrier = value != 0;
+    }
+    else if (!std::strcmp(name, "spheres_smem")) {
+        c->spheres_smem = value ? -1 : 0;
     }
     else if (!std::strcmp(name, "timeline")) {
         c->timeline = value ? 1 : 0;

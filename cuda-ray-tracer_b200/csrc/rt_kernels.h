@@ -28,6 +28,7 @@ struct WaveLaunch {
     int *dyn_slot_group;                // this GPU's slot -> group table
     int dyn_n_groups, dyn_group_rows, dyn_max_slots, dyn_ahead;
     int lone_kernel = 1;                // 1 = scenes of exactly one cubic object run the lone-cubic instantiation (option "lone_kernel")
+    int spheres_smem = -1;              // -1 = automatic, 0 = never stage the FP32 sphere records in shared memory (option "spheres_smem")
 };
 // (re)initialise a slot -> group table: the first `ahead` slots statically, the rest "not fetched yet"
 cudaError_t launch_dyn_table_init(int *slot_group, int max_slots, int ahead, int n_groups, int rank, int world, cudaStream_t stream);

@@ -323,7 +323,7 @@ render_wave_kernel(const __grid_constant__ SceneView g_param, const __grid_const
         // ---- phase A + B: nearest hit, hit record, compact hit list ---------------------------------------
         int obj = -1;
         if (active) {
-            Hit h = nearest_hit_wave<CUBIC, GRID>(g, s, cfg, o, d, primary, !primary || prim_filter, tl);
+            Hit h = nearest_hit_wave<CUBIC, GRID, (W >= 512)>(g, s, cfg, o, d, primary, !primary || prim_filter, tl);
             if (h.slot >= 0) {
                 obj = h.orig;
                 const d3 p = d3{o.x + h.t * d.x, o.y + h.t * d.y, o.z + h.t * d.z};
@@ -446,7 +446,7 @@ render_wave_kernel(const __grid_constant__ SceneView g_param, const __grid_const
                             else if (cs >= 0) occ = blocks(intersect_slot(g, s, cs, so, sd, tl), max_t);
                         }
                         if (!occ) {
-                            const int by = occluder_wave<CUBIC, GRID>(g, s, cfg, ctl, so, sd, max_t, l.is_spherical != 0, k, l0 + j, cached_cubic, tl);
+                            const int by = occluder_wave<CUBIC, GRID, (W >= 512)>(g, s, cfg, ctl, so, sd, max_t, l.is_spherical != 0, k, l0 + j, cached_cubic, tl);
                             occ = by >= 0;
                             if (occ && cfg.use_shadow_cache) ctl.shadow_cache[j] = by;   // benign race: any occluder will do
                         }
@@ -686,6 +686,7 @@ cudaError_t launch_render_wave_t(const SceneView &scene, const FrameParams &fram
     // room for three CTAs per SM; rays the walker refuses (rt_grid.cuh: grid_ray_ok) run the brute-force loop from L2
     cfg.use_grid = (wl.accel && scene.grid.cell_start != nullptr && scene.n_sphere > 0) ? 1 : 0;
     cfg.spheres_in_smem = cfg.use_grid ? 0 : 1;
+    if (wl.spheres_smem == 0) cfg.spheres_in_smem = 0;   // option "spheres_smem": read the FP32 sphere records through L1 instead
     size_t scene_smem = wave_scene_smem(scene, cfg.spheres_in_smem != 0);
     if (cfg.spheres_in_smem && wave_fixed_smem<512>() + scene_smem + wave_cubic_smem(scene, 512) > (size_t) max_smem) {
         cfg.spheres_in_smem = 0;
